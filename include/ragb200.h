@@ -1,0 +1,143 @@
+/* ragb200.h — C ABI of the B200-native embedding store + exact top-k search.
+ *
+ * Drop-in boundary for the retrieval hot path of modular-rag-system.  The
+ * reference has no FFI of its own (it is pure Python); each entry point below
+ * names the reference method whose arithmetic it replaces (file:line under the
+ * reference tree).  The ctypes binding a maintainer would add is shown in
+ * INTEGRATION.md and implemented in modular-rag-system_b200/_lib.py.
+ *
+ * Conventions
+ *   - every function returns 0 on success, a negative RAGB_E* code on failure;
+ *     ragb_last_error() gives a thread-local message.  Nothing throws.
+ *   - "host" entry points take plain host pointers and copy; "_dev" entry
+ *     points take device pointers on the store's GPU plus a cudaStream_t passed
+ *     as void* (NULL = the store's own stream, synchronised before return).
+ *   - result slots: k per query, best first; unused slots hold id -1 and
+ *     score -inf.  Order: score descending, then larger row id first (the
+ *     reference's stable sort over "ORDER BY timestamp DESC" rows,
+ *     ollama_rag_system.py:474,512).
+ *   - there is no CPU fallback: without a CUDA device every compute entry point
+ *     fails with RAGB_ECUDA.
+ */
+#ifndef RAGB200_H
+#define RAGB200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RAGB_ABI_VERSION 1
+
+/* element types */
+#define RAGB_F16 0
+#define RAGB_BF16 1
+#define RAGB_F32 2
+/* mask element types for ragb_store_add_pooled* */
+#define RAGB_MASK_U8 0
+#define RAGB_MASK_I32 1
+#define RAGB_MASK_I64 2
+#define RAGB_MASK_F32 3
+/* metrics */
+#define RAGB_IP 0      /* inner product over the stored (unit) rows            */
+#define RAGB_COSINE 1  /* ollama_rag_system.py:199-222: q.x/(|q||x|), 0 if a norm is 0 */
+/* search flags */
+#define RAGB_CLAMP01 1      /* clamp scores to [0,1] before ranking (:218)        */
+#define RAGB_FORCE_SCAN 2   /* use the bandwidth-bound scan kernel per query      */
+#define RAGB_FORCE_GEMM 4   /* use the tcgen05 batched kernel even for nq == 1    */
+#define RAGB_NO_RESCORE 8   /* batched path: skip the fp32 re-score of the winners */
+
+/* error codes */
+#define RAGB_OK 0
+#define RAGB_EINVAL -1
+#define RAGB_ECUDA -2
+#define RAGB_ENOMEM -3
+#define RAGB_EFULL -4
+#define RAGB_EUNSUPPORTED -5
+
+typedef struct ragb_store ragb_store;
+
+/* ---- library ----------------------------------------------------------- */
+int ragb_abi_version(void);
+const char* ragb_last_error(void);
+/* number of CUDA kernels this library has launched in this process */
+int64_t ragb_launch_count(void);
+int ragb_device_count(void);
+
+/* ---- store life cycle --------------------------------------------------
+ * Replaces the in-memory index slot of RAGVectorStore (faiss.IndexFlatIP,
+ * ollama_rag_system.py:298-305): a device-resident row-major matrix of unit
+ * rows (fp16 / bf16 / fp32) + the fp32 norm each row had before normalising. */
+int ragb_store_create(int device, int dim, int dtype, int64_t capacity, ragb_store** out);
+int ragb_store_destroy(ragb_store* s);
+int ragb_store_reserve(ragb_store* s, int64_t capacity); /* grow, keeps rows */
+int ragb_store_clear(ragb_store* s);
+int64_t ragb_store_size(const ragb_store* s);
+int64_t ragb_store_capacity(const ragb_store* s);
+int ragb_store_dim(const ragb_store* s);
+int ragb_store_ld(const ragb_store* s); /* row stride in elements */
+int ragb_store_dtype(const ragb_store* s);
+int ragb_store_device(const ragb_store* s);
+void* ragb_store_rows_dev(const ragb_store* s);  /* device pointer to the packed rows */
+float* ragb_store_norms_dev(const ragb_store* s);
+
+/* ---- ingest --------------------------------------------------------------
+ * ragb_store_add*: RAGVectorStore._update_faiss_index, ollama_rag_system.py:372-386
+ *   (fp32 normalise :379-380, append :382, row number returned for
+ *   document_mapping :383).  A zero row packs to zeros with norm 0 (search
+ *   semantics :214-215) instead of the reference's NaN row.
+ * ragb_store_add_pooled*: the encoder tail inside SentenceTransformer.encode
+ *   (call sites embedding_pipeline.py:424, ollama_rag_system.py:163): masked
+ *   mean over tokens, L2 normalise, pack. */
+int ragb_store_add(ragb_store* s, const float* rows, int64_t n, int64_t* out_first_row);
+int ragb_store_add_dev(ragb_store* s, const void* rows, int in_dtype, int64_t n, int64_t ld_in,
+                       int64_t* out_first_row, void* stream);
+int ragb_store_set(ragb_store* s, int64_t row, const float* vec); /* INSERT OR REPLACE, :351 */
+int ragb_store_add_pooled(ragb_store* s, const void* tok, int tok_dtype, const void* mask,
+                          int mask_dtype, int64_t batch, int seq, int hidden,
+                          int64_t* out_first_row);
+int ragb_store_add_pooled_dev(ragb_store* s, const void* tok, int tok_dtype, const void* mask,
+                              int mask_dtype, int64_t batch, int seq, int hidden,
+                              int64_t* out_first_row, void* stream);
+/* stateless kernels (device pointers): pack into caller-owned rows */
+int ragb_norm_pack_dev(int device, const void* in, int in_dtype, int64_t n, int dim, int64_t ld_in,
+                       void* out, int out_dtype, int64_t ld_out, float* out_norms, void* stream);
+int ragb_pool_norm_pack_dev(int device, const void* tok, int tok_dtype, const void* mask,
+                            int mask_dtype, int64_t batch, int seq, int hidden, void* out,
+                            int out_dtype, int64_t ld_out, float* out_norms, void* stream);
+/* copy rows [row0,row0+n) back to the host (packed elements, ld = dim) and their norms */
+int ragb_store_get_rows(ragb_store* s, int64_t row0, int64_t n, void* out_rows, float* out_norms);
+
+/* ---- search ----------------------------------------------------------------
+ * Replaces the scan / threshold / sort / slice of RAGVectorStore._search_sqlite
+ * (ollama_rag_system.py:480-515) and EmbeddingGenerator.calculate_similarity
+ * (:199-222) over rows [row_begin,row_end) (row_end < 0 = all rows).
+ *   valid  : optional per-row uint8 (host for ragb_search, device for _dev),
+ *            0 = skip the row (NULL embedding :485-492, source filter :466-469,
+ *            window :474, replaced ids :351).
+ *   keep a row when score >= threshold (:495); pass -INFINITY for none. */
+int ragb_search(ragb_store* s, const float* q, int64_t nq, int k, int metric, float threshold,
+                int flags, int64_t row_begin, int64_t row_end, const uint8_t* valid,
+                float* out_scores, int64_t* out_ids);
+int ragb_search_dev(ragb_store* s, const float* q, int64_t nq, int k, int metric, float threshold,
+                    int flags, int64_t row_begin, int64_t row_end, const uint8_t* valid,
+                    float* out_scores, int64_t* out_ids, void* stream);
+
+/* ---- multi-GPU building blocks (row-sharded corpus, one process per GPU) ----
+ * local top-k as sortable 64-bit keys: (ordered score bits << 32) | (row + id_base),
+ * kpad = ragb_kpad(k) keys per query, sorted best first, 0 = empty slot.
+ * The keys of all ranks are all-gathered (NCCL) and merged with ragb_merge_keys_dev. */
+int ragb_kpad(int k);
+int ragb_search_keys_dev(ragb_store* s, const float* q, int64_t nq, int k, int metric,
+                         float threshold, int flags, int64_t row_begin, int64_t row_end,
+                         const uint8_t* valid, uint32_t id_base, uint64_t* out_keys, void* stream);
+/* keys: n_lists lists per query; list (q,p) starts at keys + q*stride_q + p*stride_p */
+int ragb_merge_keys_dev(int device, const uint64_t* keys, int64_t nq, int n_lists, int kpad,
+                        int64_t stride_q, int64_t stride_p, int k, float* out_scores,
+                        int64_t* out_ids, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RAGB200_H */

@@ -1,0 +1,10 @@
+"""B200-native exact vector retrieval for modular-rag-system (sm_100a only).
+
+``DeviceStore``      device-resident embedding store + exact top-k search (C ABI: include/ragb200.h)
+``B200VectorStore``  drop-in for the reference's ``RAGVectorStore`` (ollama_rag_system.py:225-554)
+``ShardedSearcher``  row-sharded multi-GPU search, one process per GPU (torch.distributed / NCCL)
+"""
+from ._lib import RagbError, build, lib  # noqa: F401
+from .store import DeviceStore, kpad_of, launch_count, merge_keys_dev  # noqa: F401
+
+__all__ = ["DeviceStore", "RagbError", "build", "lib", "kpad_of", "launch_count", "merge_keys_dev"]

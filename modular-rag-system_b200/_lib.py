@@ -1,0 +1,97 @@
+"""ctypes binding of include/ragb200.h (libragb200.so, built in-tree for sm_100a).
+
+This is the binding INTEGRATION.md shows a maintainer of the reference adding; there
+is no CPU fallback — if the shared library is missing, loading fails loudly.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+from pathlib import Path
+
+CSRC = Path(__file__).resolve().parent / "csrc"
+LIB_PATH = CSRC / "libragb200.so"
+
+F16, BF16, F32 = 0, 1, 2
+MASK_U8, MASK_I32, MASK_I64, MASK_F32 = 0, 1, 2, 3
+IP, COSINE = 0, 1
+CLAMP01, FORCE_SCAN, FORCE_GEMM, NO_RESCORE = 1, 2, 4, 8
+OK, EINVAL, ECUDA, ENOMEM, EFULL, EUNSUPPORTED = 0, -1, -2, -3, -4, -5
+
+_vp, _i, _i64, _f = C.c_void_p, C.c_int, C.c_int64, C.c_float
+_pi64 = C.POINTER(C.c_int64)
+
+# name -> (restype, argtypes); every symbol include/ragb200.h declares
+SIGNATURES = {
+    "ragb_abi_version": (_i, []),
+    "ragb_last_error": (C.c_char_p, []),
+    "ragb_launch_count": (_i64, []),
+    "ragb_device_count": (_i, []),
+    "ragb_store_create": (_i, [_i, _i, _i, _i64, C.POINTER(_vp)]),
+    "ragb_store_destroy": (_i, [_vp]),
+    "ragb_store_reserve": (_i, [_vp, _i64]),
+    "ragb_store_clear": (_i, [_vp]),
+    "ragb_store_size": (_i64, [_vp]),
+    "ragb_store_capacity": (_i64, [_vp]),
+    "ragb_store_dim": (_i, [_vp]),
+    "ragb_store_ld": (_i, [_vp]),
+    "ragb_store_dtype": (_i, [_vp]),
+    "ragb_store_device": (_i, [_vp]),
+    "ragb_store_rows_dev": (_vp, [_vp]),
+    "ragb_store_norms_dev": (_vp, [_vp]),
+    "ragb_store_add": (_i, [_vp, _vp, _i64, _pi64]),
+    "ragb_store_add_dev": (_i, [_vp, _vp, _i, _i64, _i64, _pi64, _vp]),
+    "ragb_store_set": (_i, [_vp, _i64, _vp]),
+    "ragb_store_add_pooled": (_i, [_vp, _vp, _i, _vp, _i, _i64, _i, _i, _pi64]),
+    "ragb_store_add_pooled_dev": (_i, [_vp, _vp, _i, _vp, _i, _i64, _i, _i, _pi64, _vp]),
+    "ragb_norm_pack_dev": (_i, [_i, _vp, _i, _i64, _i, _i64, _vp, _i, _i64, _vp, _vp]),
+    "ragb_pool_norm_pack_dev": (_i, [_i, _vp, _i, _vp, _i, _i64, _i, _i, _vp, _i, _i64, _vp, _vp]),
+    "ragb_store_get_rows": (_i, [_vp, _i64, _i64, _vp, _vp]),
+    "ragb_search": (_i, [_vp, _vp, _i64, _i, _i, _f, _i, _i64, _i64, _vp, _vp, _vp]),
+    "ragb_search_dev": (_i, [_vp, _vp, _i64, _i, _i, _f, _i, _i64, _i64, _vp, _vp, _vp, _vp]),
+    "ragb_kpad": (_i, [_i]),
+    "ragb_search_keys_dev": (_i, [_vp, _vp, _i64, _i, _i, _f, _i, _i64, _i64, _vp, C.c_uint32, _vp, _vp]),
+    "ragb_merge_keys_dev": (_i, [_i, _vp, _i64, _i, _i, _i64, _i64, _i, _vp, _vp, _vp]),
+}
+
+
+class RagbError(RuntimeError):
+    def __init__(self, code: int, msg: str):
+        super().__init__(f"ragb200 error {code}: {msg}")
+        self.code = code
+
+
+def build(force: bool = False) -> Path:
+    """Compile csrc/ragb200.cu -> csrc/libragb200.so for sm_100a (nvcc cross-compiles without a GPU)."""
+    srcs = list(CSRC.glob("*.cu")) + list(CSRC.glob("*.cuh")) + [CSRC.parent.parent / "include" / "ragb200.h"]
+    if not force and LIB_PATH.exists() and all(LIB_PATH.stat().st_mtime >= s.stat().st_mtime for s in srcs):
+        return LIB_PATH
+    subprocess.run(["bash", str(CSRC / "build.sh")], check=True)
+    return LIB_PATH
+
+
+_lib = None
+
+
+def lib() -> C.CDLL:
+    """The loaded library.  Raises if it has not been built: no fallback exists."""
+    global _lib
+    if _lib is None:
+        if not LIB_PATH.exists():
+            raise ImportError(
+                f"{LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                "(or modular-rag-system_b200/csrc/build.sh).  There is no CPU fallback.")
+        l = C.CDLL(str(LIB_PATH))
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(l, name)
+            fn.restype, fn.argtypes = res, args
+        if l.ragb_abi_version() != 1:
+            raise ImportError("libragb200.so ABI version mismatch; rebuild")
+        _lib = l
+    return _lib
+
+
+def check(code: int) -> None:
+    if code != 0:
+        raise RagbError(code, lib().ragb_last_error().decode("utf-8", "replace"))

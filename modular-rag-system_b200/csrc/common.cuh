@@ -1,0 +1,196 @@
+// common.cuh — sortable keys, warp-level top-k lists, load helpers (sm_100a).
+#pragma once
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace ragb {
+
+constexpr int kStage = 64;  // per-warp staging slots for candidates awaiting a merge
+
+// ---------------------------------------------------------------------------
+// 64-bit candidate key: (order-preserving score bits << 32) | row id.
+// Larger key == better candidate: higher score first, then larger (newer) row
+// id (ollama_rag_system.py:474,512).  0 is "empty" and below every real key.
+// ---------------------------------------------------------------------------
+__host__ __device__ __forceinline__ uint32_t order_bits(float s) {
+  uint32_t b;
+#ifdef __CUDA_ARCH__
+  b = __float_as_uint(s);
+#else
+  union { float f; uint32_t u; } c; c.f = s; b = c.u;
+#endif
+  return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+}
+__host__ __device__ __forceinline__ float unorder_bits(uint32_t o) {
+  uint32_t b = (o & 0x80000000u) ? (o & 0x7fffffffu) : ~o;
+#ifdef __CUDA_ARCH__
+  return __uint_as_float(b);
+#else
+  union { float f; uint32_t u; } c; c.u = b; return c.f;
+#endif
+}
+__device__ __forceinline__ uint64_t make_key(float s, uint32_t id) {
+  if (s != s) s = -INFINITY;  // NaN ranks last
+  return ((uint64_t)order_bits(s) << 32) | id;
+}
+__device__ __forceinline__ float key_score(uint64_t k) { return unorder_bits((uint32_t)(k >> 32)); }
+__device__ __forceinline__ uint32_t key_id(uint64_t k) { return (uint32_t)k; }
+
+// score post-processing shared by every search kernel
+__device__ __forceinline__ float finish_score(float dot, float scale, int flags) {
+  float s = dot * scale;
+  if (flags & 1) s = fminf(fmaxf(s, 0.0f), 1.0f);  // RAGB_CLAMP01, :218
+  return s;
+}
+
+// smallest power of two >= k, at least 16
+__host__ __device__ inline int kpad_of(int k) {
+  int p = 16;
+  while (p < k) p <<= 1;
+  return p;
+}
+// per-warp list buffer length: the sorted list [0,kpad) plus room for the
+// staging area / a second list at the tail
+__host__ __device__ inline int listbuf_len(int kpad) { return kpad >= kStage ? 2 * kpad : 2 * kStage; }
+
+// ---------------------------------------------------------------------------
+// Warp-level bitonic primitives on a shared-memory array of 64-bit keys.
+// ---------------------------------------------------------------------------
+// full bitonic sort of buf[0,n) (n power of two), ascending or descending
+__device__ __forceinline__ void warp_bitonic_sort(uint64_t* buf, int n, bool descending, int lane) {
+  for (int size = 2; size <= n; size <<= 1) {
+    for (int stride = size >> 1; stride > 0; stride >>= 1) {
+      __syncwarp();
+      for (int t = lane; t < (n >> 1); t += 32) {
+        int lo = 2 * t - (t & (stride - 1));
+        int hi = lo + stride;
+        bool up = ((lo & size) == 0);  // direction of this sub-sequence
+        if (descending) up = !up;
+        uint64_t a = buf[lo], b = buf[hi];
+        if ((a > b) == up) { buf[lo] = b; buf[hi] = a; }
+      }
+    }
+  }
+  __syncwarp();
+}
+// buf[0,n) is bitonic (descending run then ascending run); sort it descending
+__device__ __forceinline__ void warp_bitonic_merge_desc(uint64_t* buf, int n, int lane) {
+  for (int stride = n >> 1; stride > 0; stride >>= 1) {
+    __syncwarp();
+    for (int t = lane; t < (n >> 1); t += 32) {
+      int lo = 2 * t - (t & (stride - 1));
+      int hi = lo + stride;
+      uint64_t a = buf[lo], b = buf[hi];
+      if (a < b) { buf[lo] = b; buf[hi] = a; }
+    }
+  }
+  __syncwarp();
+}
+
+// A warp's running top-k: buf[0,kpad) sorted descending, staging area at
+// buf[len-kStage,len) filled from its start, `cnt` staged keys (warp-uniform).
+struct WarpTopK {
+  uint64_t* buf;
+  int kpad, len, k;
+  int cnt;
+  uint64_t thr;  // key of the k-th best so far (0 while fewer than k are held)
+
+  __device__ __forceinline__ void init(uint64_t* b, int k_, int kpad_, int lane) {
+    buf = b; k = k_; kpad = kpad_; len = listbuf_len(kpad_); cnt = 0; thr = 0;
+    for (int i = lane; i < len; i += 32) buf[i] = 0;
+    __syncwarp();
+  }
+  // merge the staged keys into the list and refresh the threshold
+  __device__ __forceinline__ void flush(int lane) {
+    if (cnt == 0) return;
+    uint64_t* st = buf + (len - kStage);
+    __syncwarp();
+    for (int i = cnt + lane; i < kStage; i += 32) st[i] = 0;
+    warp_bitonic_sort(st, kStage, /*descending=*/false, lane);
+    // the middle (between the list and the staging area) is already zero
+    warp_bitonic_merge_desc(buf, len, lane);
+    for (int i = kpad + lane; i < len; i += 32) buf[i] = 0;
+    __syncwarp();
+    thr = buf[k - 1];
+    cnt = 0;
+  }
+  // warp-collective: lanes with pred push `key`; call with all 32 lanes
+  __device__ __forceinline__ void push(bool pred, uint64_t key, int lane) {
+    unsigned m = __ballot_sync(0xffffffffu, pred);
+    if (m == 0) return;
+    int n = __popc(m);
+    if (cnt + n > kStage) flush(lane);  // cnt <= 32 afterwards, n <= 32
+    if (pred) {
+      // staged keys may be stale against a threshold tightened by the flush: harmless
+      int pos = cnt + __popc(m & ((1u << lane) - 1));
+      buf[len - kStage + pos] = key;
+    }
+    cnt += n;
+    __syncwarp();
+    if (cnt >= 32) flush(lane);
+  }
+  // fold another sorted-descending list of kpad keys (shared or global) into this one
+  __device__ __forceinline__ void merge_list(const uint64_t* other, int lane) {
+    flush(lane);
+    for (int i = lane; i < kpad; i += 32) buf[len - 1 - i] = other[i];
+    warp_bitonic_merge_desc(buf, len, lane);
+    for (int i = kpad + lane; i < len; i += 32) buf[i] = 0;
+    __syncwarp();
+    thr = buf[k - 1];
+  }
+};
+
+// ---------------------------------------------------------------------------
+// element helpers
+// ---------------------------------------------------------------------------
+template <typename T> struct Elem;
+template <> struct Elem<__half> {
+  static constexpr int per16 = 8;
+  __device__ static __forceinline__ void unpack(const uint4& v, float* f) {
+    const __half2* h = reinterpret_cast<const __half2*>(&v);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) { float2 t = __half22float2(h[i]); f[2 * i] = t.x; f[2 * i + 1] = t.y; }
+  }
+  __device__ static __forceinline__ __half from_float(float x) { return __float2half_rn(x); }
+  __device__ static __forceinline__ float to_float(__half x) { return __half2float(x); }
+};
+template <> struct Elem<__nv_bfloat16> {
+  static constexpr int per16 = 8;
+  __device__ static __forceinline__ void unpack(const uint4& v, float* f) {
+    const uint32_t* w = reinterpret_cast<const uint32_t*>(&v);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      f[2 * i] = __uint_as_float(w[i] << 16);
+      f[2 * i + 1] = __uint_as_float(w[i] & 0xffff0000u);
+    }
+  }
+  __device__ static __forceinline__ __nv_bfloat16 from_float(float x) { return __float2bfloat16_rn(x); }
+  __device__ static __forceinline__ float to_float(__nv_bfloat16 x) { return __bfloat162float(x); }
+};
+template <> struct Elem<float> {
+  static constexpr int per16 = 4;
+  __device__ static __forceinline__ void unpack(const uint4& v, float* f) {
+    f[0] = __uint_as_float(v.x); f[1] = __uint_as_float(v.y);
+    f[2] = __uint_as_float(v.z); f[3] = __uint_as_float(v.w);
+  }
+  __device__ static __forceinline__ float from_float(float x) { return x; }
+  __device__ static __forceinline__ float to_float(float x) { return x; }
+};
+
+// streaming 128-bit load: read-only path, do not allocate in L1
+__device__ __forceinline__ uint4 ld_stream16(const void* p) {
+  uint4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+  return r;
+}
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+}  // namespace ragb

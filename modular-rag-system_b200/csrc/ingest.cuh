@@ -1,0 +1,201 @@
+// ingest.cuh — K2 norm_pack and K1 pool_norm_pack (sm_100a, HBM-bound).
+//
+// K2: RAGVectorStore._update_faiss_index, ollama_rag_system.py:379-380 —
+//     e = float32(x); e = e / ||e||  -> packed fp16/bf16/fp32 row + fp32 norm.
+//     A zero row packs to zeros (norm 0): search semantics :214-215.
+// K1: encoder tail of SentenceTransformer.encode (call sites
+//     embedding_pipeline.py:424, ollama_rag_system.py:163; sentence-transformers
+//     Pooling(mean) + Normalize):  v = sum_s m_s h_s / max(sum_s m_s, 1e-9);
+//     v / max(||v||, 1e-12) -> packed row + fp32 norm.  Tokens with m_s == 0 are
+//     never fetched from HBM.
+#pragma once
+#include "common.cuh"
+
+namespace ragb {
+
+// 8 consecutive elements [8c, 8c+8) of a row of `dim` elements as fp32, zero filled
+template <typename T>
+__device__ __forceinline__ void load8(const T* row, int c, int dim, bool vec_ok, float* f) {
+  const int e0 = c * 8;
+  if (vec_ok && e0 + 8 <= dim) {
+    if constexpr (sizeof(T) == 2) {
+      uint4 v = *reinterpret_cast<const uint4*>(row + e0);
+      Elem<T>::unpack(v, f);
+    } else {
+      float4 a = *reinterpret_cast<const float4*>(row + e0);
+      float4 b = *reinterpret_cast<const float4*>(row + e0 + 4);
+      f[0] = a.x; f[1] = a.y; f[2] = a.z; f[3] = a.w; f[4] = b.x; f[5] = b.y; f[6] = b.z; f[7] = b.w;
+    }
+  } else {
+#pragma unroll
+    for (int e = 0; e < 8; ++e) f[e] = (e0 + e < dim) ? Elem<T>::to_float(row[e0 + e]) : 0.f;
+  }
+}
+// streaming variant for data touched once
+template <typename T>
+__device__ __forceinline__ void load8_stream(const T* row, int c, int dim, bool vec_ok, float* f) {
+  const int e0 = c * 8;
+  if (vec_ok && e0 + 8 <= dim) {
+    if constexpr (sizeof(T) == 2) {
+      uint4 v = ld_stream16(row + e0);
+      Elem<T>::unpack(v, f);
+    } else {
+      uint4 a = ld_stream16(row + e0), b = ld_stream16(row + e0 + 4);
+      Elem<float>::unpack(a, f); Elem<float>::unpack(b, f + 4);
+    }
+  } else {
+#pragma unroll
+    for (int e = 0; e < 8; ++e) f[e] = (e0 + e < dim) ? Elem<T>::to_float(row[e0 + e]) : 0.f;
+  }
+}
+// 8 elements to a 16-byte aligned packed row (ld is a multiple of 8)
+template <typename T>
+__device__ __forceinline__ void store8(T* row, int c, const float* f) {
+  if constexpr (sizeof(T) == 2) {
+    union { uint4 v; T h[8]; } u;
+#pragma unroll
+    for (int e = 0; e < 8; ++e) u.h[e] = Elem<T>::from_float(f[e]);
+    *reinterpret_cast<uint4*>(row + c * 8) = u.v;
+  } else {
+    *reinterpret_cast<float4*>(row + c * 8) = make_float4(f[0], f[1], f[2], f[3]);
+    *reinterpret_cast<float4*>(row + c * 8 + 4) = make_float4(f[4], f[5], f[6], f[7]);
+  }
+}
+
+// ---- K2 -------------------------------------------------------------------
+template <typename Tin, typename Tout>
+__global__ void __launch_bounds__(256) norm_pack_kernel(const Tin* __restrict__ in, int64_t n, int dim,
+                                                        int64_t ld_in, Tout* __restrict__ out,
+                                                        int64_t ld_out, float* __restrict__ norms,
+                                                        bool vec_ok) {
+  const int lane = threadIdx.x & 31;
+  const int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (row >= n) return;
+  const Tin* src = in + row * ld_in;
+  Tout* dst = out + row * ld_out;
+  const int chunks_in = (dim + 7) / 8, chunks_out = (int)(ld_out / 8);
+  float ss = 0.f;
+  for (int c = lane; c < chunks_in; c += 32) {
+    float f[8];
+    load8(src, c, dim, vec_ok, f);
+#pragma unroll
+    for (int e = 0; e < 8; ++e) ss = fmaf(f[e], f[e], ss);
+  }
+  ss = warp_sum(ss);
+  const float nrm = sqrtf(ss);
+  for (int c = lane; c < chunks_out; c += 32) {
+    float f[8];
+    if (c < chunks_in) load8(src, c, dim, vec_ok, f);
+    else {
+#pragma unroll
+      for (int e = 0; e < 8; ++e) f[e] = 0.f;
+    }
+#pragma unroll
+    for (int e = 0; e < 8; ++e) f[e] = nrm > 0.f ? __fdiv_rn(f[e], nrm) : 0.f;
+    store8(dst, c, f);
+  }
+  if (lane == 0 && norms) norms[row] = nrm;
+}
+
+// ---- K1 -------------------------------------------------------------------
+template <typename Tm> __device__ __forceinline__ float mask_weight(Tm m) { return (float)m; }
+
+// block-wide sum, deterministic; red = 8 floats of shared memory
+__device__ __forceinline__ float block_sum(float v, float* red) {
+  v = warp_sum(v);
+  __syncthreads();
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
+  __syncthreads();
+  float t = 0.f;
+  for (int w = 0; w < (int)(blockDim.x >> 5); ++w) t += red[w];
+  return t;
+}
+
+constexpr int kPoolThreads = 256;
+constexpr int kPoolUnroll = 8;
+
+// dynamic shared memory: float w[seq] | float acc[groups][W][8] | float v[chunks*8] | float red[8]
+template <typename Tin, typename Tm, typename Tout>
+__global__ void __launch_bounds__(kPoolThreads) pool_norm_pack_kernel(
+    const Tin* __restrict__ tok, const Tm* __restrict__ mask, int seq, int hidden,
+    Tout* __restrict__ out, int64_t ld_out, float* __restrict__ norms, bool vec_ok) {
+  extern __shared__ __align__(16) float sm[];
+  const int chunks = (hidden + 7) / 8;
+  const int W = chunks < kPoolThreads ? chunks : kPoolThreads;
+  const int groups = kPoolThreads / W;
+  float* w = sm;
+  float* accs = w + ((seq + 3) & ~3);
+  float* v = accs + (size_t)groups * W * 8;
+  float* red = v + (size_t)chunks * 8;
+  const int64_t b = blockIdx.x;
+  const int t = threadIdx.x;
+
+  float wsum = 0.f;
+  for (int s = t; s < seq; s += kPoolThreads) {
+    float m = mask ? mask_weight(mask[b * seq + s]) : 1.0f;
+    w[s] = m;
+    wsum += m;
+  }
+  wsum = block_sum(wsum, red);  // includes the barrier that publishes w[]
+  const float inv_cnt = 1.0f / fmaxf(wsum, 1e-9f);
+
+  const int g = t / W, col = t - g * W;
+  const bool active = g < groups;
+  const Tin* base = tok + (size_t)b * seq * hidden;
+  for (int c0 = 0; c0 < chunks; c0 += W) {
+    const int c = c0 + col;
+    float acc[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) acc[e] = 0.f;
+    if (active && c < chunks) {
+      for (int s0 = g; s0 < seq; s0 += groups * kPoolUnroll) {
+        float f[kPoolUnroll][8];
+        float ws[kPoolUnroll];
+#pragma unroll
+        for (int u = 0; u < kPoolUnroll; ++u) {
+          const int s = s0 + u * groups;
+          ws[u] = s < seq ? w[s] : 0.f;
+          if (ws[u] != 0.f) load8_stream(base + (size_t)s * hidden, c, hidden, vec_ok, f[u]);
+          else {
+#pragma unroll
+            for (int e = 0; e < 8; ++e) f[u][e] = 0.f;
+          }
+        }
+#pragma unroll
+        for (int u = 0; u < kPoolUnroll; ++u)
+#pragma unroll
+          for (int e = 0; e < 8; ++e) acc[e] = fmaf(ws[u], f[u][e], acc[e]);
+      }
+    }
+    __syncthreads();
+    if (active) {
+#pragma unroll
+      for (int e = 0; e < 8; ++e) accs[((size_t)g * W + col) * 8 + e] = acc[e];
+    }
+    __syncthreads();
+    if (t < W && c0 + t < chunks) {
+#pragma unroll
+      for (int e = 0; e < 8; ++e) {
+        float s = 0.f;
+        for (int gg = 0; gg < groups; ++gg) s += accs[((size_t)gg * W + t) * 8 + e];
+        v[(size_t)(c0 + t) * 8 + e] = s * inv_cnt;
+      }
+    }
+  }
+  __syncthreads();
+  float ss = 0.f;
+  for (int i = t; i < chunks * 8; i += kPoolThreads) ss = fmaf(v[i], v[i], ss);
+  ss = block_sum(ss, red);
+  const float nrm = sqrtf(ss);
+  const float den = fmaxf(nrm, 1e-12f);
+  Tout* dst = out + b * ld_out;
+  for (int c = t; c < (int)(ld_out / 8); c += kPoolThreads) {
+    float f[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) f[e] = c < chunks ? __fdiv_rn(v[(size_t)c * 8 + e], den) : 0.f;
+    store8(dst, c, f);
+  }
+  if (t == 0 && norms) norms[b] = nrm;
+}
+
+}  // namespace ragb

@@ -1,0 +1,638 @@
+// ragb200.cu — C ABI (include/ragb200.h) over the sm_100a kernels.
+// Host logic only: store life cycle, dispatch, workspaces.  No torch types, no CPU fallback.
+#include "../../include/ragb200.h"
+
+#include <algorithm>
+#include <atomic>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "common.cuh"
+#include "gemm_topk.cuh"
+#include "ingest.cuh"
+#include "merge.cuh"
+#include "scan.cuh"
+
+using namespace ragb;
+
+// ---------------------------------------------------------------------------
+// errors, counters
+// ---------------------------------------------------------------------------
+static thread_local std::string g_err;
+static std::atomic<int64_t> g_launches{0};
+
+static int fail(int code, const char* fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof buf, fmt, ap);
+  va_end(ap);
+  g_err = buf;
+  return code;
+}
+#define CU_TRY(expr)                                                                       \
+  do {                                                                                     \
+    cudaError_t e_ = (expr);                                                               \
+    if (e_ != cudaSuccess)                                                                 \
+      return fail(e_ == cudaErrorMemoryAllocation ? RAGB_ENOMEM : RAGB_ECUDA, "%s: %s (%s:%d)", \
+                  #expr, cudaGetErrorString(e_), __FILE__, __LINE__);                      \
+  } while (0)
+#define RB_TRY(expr)        \
+  do {                      \
+    int r_ = (expr);        \
+    if (r_ != RAGB_OK) return r_; \
+  } while (0)
+#define LAUNCHED()                   \
+  do {                               \
+    g_launches.fetch_add(1);         \
+    CU_TRY(cudaGetLastError());      \
+  } while (0)
+
+static size_t elem_size(int dtype) { return dtype == RAGB_F32 ? 4 : 2; }
+
+// ---------------------------------------------------------------------------
+// store
+// ---------------------------------------------------------------------------
+struct ragb_store {
+  int device = 0, dim = 0, dtype = 0, n_sm = 148;
+  int64_t ld = 0, capacity = 0;
+  std::atomic<int64_t> n{0};
+  void* rows = nullptr;
+  float* norms = nullptr;
+  cudaStream_t stream = nullptr;
+  std::mutex add_mu, search_mu;
+  // search workspace (guarded by search_mu)
+  void* ws = nullptr;
+  size_t ws_bytes = 0;
+  // ingest staging (guarded by add_mu)
+  void* stage_dev = nullptr;
+  size_t stage_dev_bytes = 0;
+  void* stage_host = nullptr;  // pinned
+  size_t stage_host_bytes = 0;
+  // pinned buffers for the host search entry point (guarded by search_mu)
+  void* pin = nullptr;
+  size_t pin_bytes = 0;
+  void* io = nullptr;  // device mirror of pin
+  size_t io_bytes = 0;
+  GemmState gemm;  // tensor maps etc. of the batched path
+};
+
+struct DeviceGuard {
+  int prev = -1;
+  bool ok = true;
+  explicit DeviceGuard(int dev) {
+    if (cudaGetDevice(&prev) != cudaSuccess) { ok = false; return; }
+    if (prev != dev && cudaSetDevice(dev) != cudaSuccess) ok = false;
+  }
+  ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+};
+#define ON_DEVICE(dev)                                                        \
+  DeviceGuard guard_(dev);                                                    \
+  if (!guard_.ok) return fail(RAGB_ECUDA, "cannot select CUDA device %d: %s", dev, \
+                              cudaGetErrorString(cudaGetLastError()))
+
+static int grow(void** p, size_t* have, size_t need, bool pinned) {
+  if (*have >= need) return RAGB_OK;
+  size_t want = need + need / 4;
+  if (*p) {
+    if (pinned) CU_TRY(cudaFreeHost(*p)); else CU_TRY(cudaFree(*p));
+    *p = nullptr; *have = 0;
+  }
+  if (pinned) CU_TRY(cudaMallocHost(p, want)); else CU_TRY(cudaMalloc(p, want));
+  *have = want;
+  return RAGB_OK;
+}
+
+extern "C" int ragb_abi_version(void) { return RAGB_ABI_VERSION; }
+extern "C" const char* ragb_last_error(void) { return g_err.c_str(); }
+extern "C" int64_t ragb_launch_count(void) { return g_launches.load(); }
+extern "C" int ragb_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+  return n;
+}
+extern "C" int ragb_kpad(int k) { return kpad_of(k); }
+
+static int alloc_rows(ragb_store* s, int64_t capacity, void** rows, float** norms) {
+  size_t bytes = (size_t)capacity * s->ld * elem_size(s->dtype);
+  CU_TRY(cudaMalloc(rows, bytes ? bytes : 16));
+  cudaError_t e = cudaMalloc((void**)norms, capacity ? (size_t)capacity * 4 : 16);
+  if (e != cudaSuccess) { cudaFree(*rows); *rows = nullptr; return fail(RAGB_ENOMEM, "cudaMalloc norms: %s", cudaGetErrorString(e)); }
+  return RAGB_OK;
+}
+
+extern "C" int ragb_store_create(int device, int dim, int dtype, int64_t capacity, ragb_store** out) {
+  if (!out) return fail(RAGB_EINVAL, "out is NULL");
+  *out = nullptr;
+  if (dim <= 0 || dim > 65536) return fail(RAGB_EINVAL, "dim %d out of range [1,65536]", dim);
+  if (dtype != RAGB_F16 && dtype != RAGB_BF16 && dtype != RAGB_F32) return fail(RAGB_EINVAL, "bad dtype %d", dtype);
+  if (capacity < 0 || capacity >= (int64_t)1 << 31) return fail(RAGB_EINVAL, "capacity %lld out of range [0,2^31)", (long long)capacity);
+  ON_DEVICE(device);
+  ragb_store* s = new ragb_store();
+  s->device = device; s->dim = dim; s->dtype = dtype;
+  s->ld = ((int64_t)dim + 7) / 8 * 8;
+  s->capacity = capacity;
+  cudaDeviceProp prop;
+  cudaError_t e = cudaGetDeviceProperties(&prop, device);
+  if (e != cudaSuccess) { delete s; return fail(RAGB_ECUDA, "cudaGetDeviceProperties: %s", cudaGetErrorString(e)); }
+  if (prop.major != 10) { delete s; return fail(RAGB_EUNSUPPORTED, "device %d is sm_%d%d; this library is built for sm_100a only", device, prop.major, prop.minor); }
+  s->n_sm = prop.multiProcessorCount;
+  int r = alloc_rows(s, capacity, &s->rows, &s->norms);
+  if (r != RAGB_OK) { delete s; return r; }
+  e = cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking);
+  if (e != cudaSuccess) { cudaFree(s->rows); cudaFree(s->norms); delete s; return fail(RAGB_ECUDA, "cudaStreamCreate: %s", cudaGetErrorString(e)); }
+  // padding columns must read as zero
+  cudaMemsetAsync(s->rows, 0, (size_t)capacity * s->ld * elem_size(dtype), s->stream);
+  cudaStreamSynchronize(s->stream);
+  *out = s;
+  return RAGB_OK;
+}
+
+extern "C" int ragb_store_destroy(ragb_store* s) {
+  if (!s) return RAGB_OK;
+  {
+    DeviceGuard g(s->device);
+    cudaStreamSynchronize(s->stream);
+    gemm_state_free(&s->gemm);
+    cudaFree(s->rows); cudaFree(s->norms); cudaFree(s->ws); cudaFree(s->stage_dev); cudaFree(s->io);
+    if (s->stage_host) cudaFreeHost(s->stage_host);
+    if (s->pin) cudaFreeHost(s->pin);
+    cudaStreamDestroy(s->stream);
+  }
+  delete s;
+  return RAGB_OK;
+}
+
+extern "C" int ragb_store_reserve(ragb_store* s, int64_t capacity) {
+  if (!s) return fail(RAGB_EINVAL, "store is NULL");
+  if (capacity >= (int64_t)1 << 31) return fail(RAGB_EINVAL, "capacity %lld >= 2^31", (long long)capacity);
+  std::lock_guard<std::mutex> la(s->add_mu);
+  std::lock_guard<std::mutex> ls(s->search_mu);
+  if (capacity <= s->capacity) return RAGB_OK;
+  ON_DEVICE(s->device);
+  void* rows = nullptr; float* norms = nullptr;
+  int64_t old_cap = s->capacity;
+  s->capacity = capacity;  // alloc_rows sizes from the argument, not from s
+  int r = alloc_rows(s, capacity, &rows, &norms);
+  if (r != RAGB_OK) { s->capacity = old_cap; return r; }
+  const size_t rb = (size_t)s->ld * elem_size(s->dtype);
+  const int64_t n = s->n.load();
+  cudaMemcpyAsync(rows, s->rows, (size_t)n * rb, cudaMemcpyDeviceToDevice, s->stream);
+  cudaMemsetAsync((char*)rows + (size_t)n * rb, 0, (size_t)(capacity - n) * rb, s->stream);
+  cudaMemcpyAsync(norms, s->norms, (size_t)n * 4, cudaMemcpyDeviceToDevice, s->stream);
+  cudaError_t e = cudaStreamSynchronize(s->stream);
+  if (e != cudaSuccess) { cudaFree(rows); cudaFree(norms); s->capacity = old_cap; return fail(RAGB_ECUDA, "reserve copy: %s", cudaGetErrorString(e)); }
+  cudaFree(s->rows); cudaFree(s->norms);
+  s->rows = rows; s->norms = norms;
+  gemm_state_free(&s->gemm);  // tensor maps point at the old allocation
+  return RAGB_OK;
+}
+
+extern "C" int ragb_store_clear(ragb_store* s) {
+  if (!s) return fail(RAGB_EINVAL, "store is NULL");
+  std::lock_guard<std::mutex> la(s->add_mu);
+  std::lock_guard<std::mutex> ls(s->search_mu);
+  s->n.store(0);
+  return RAGB_OK;
+}
+extern "C" int64_t ragb_store_size(const ragb_store* s) { return s ? s->n.load(std::memory_order_acquire) : 0; }
+extern "C" int64_t ragb_store_capacity(const ragb_store* s) { return s ? s->capacity : 0; }
+extern "C" int ragb_store_dim(const ragb_store* s) { return s ? s->dim : 0; }
+extern "C" int ragb_store_ld(const ragb_store* s) { return s ? (int)s->ld : 0; }
+extern "C" int ragb_store_dtype(const ragb_store* s) { return s ? s->dtype : -1; }
+extern "C" int ragb_store_device(const ragb_store* s) { return s ? s->device : -1; }
+extern "C" void* ragb_store_rows_dev(const ragb_store* s) { return s ? s->rows : nullptr; }
+extern "C" float* ragb_store_norms_dev(const ragb_store* s) { return s ? s->norms : nullptr; }
+
+// ---------------------------------------------------------------------------
+// ingest: K2 / K1 dispatch
+// ---------------------------------------------------------------------------
+template <typename Tin, typename Tout>
+static int norm_pack_launch(const void* in, int64_t n, int dim, int64_t ld_in, void* out, int64_t ld_out,
+                            float* norms, cudaStream_t st) {
+  const bool vec_ok = ((uintptr_t)in % 16 == 0) && ((ld_in * sizeof(Tin)) % 16 == 0);
+  const int rows_per_cta = 8;
+  const int64_t grid = (n + rows_per_cta - 1) / rows_per_cta;
+  norm_pack_kernel<Tin, Tout><<<(unsigned)grid, 256, 0, st>>>((const Tin*)in, n, dim, ld_in, (Tout*)out, ld_out, norms, vec_ok);
+  LAUNCHED();
+  return RAGB_OK;
+}
+template <typename Tin>
+static int norm_pack_out(const void* in, int64_t n, int dim, int64_t ld_in, void* out, int out_dtype,
+                         int64_t ld_out, float* norms, cudaStream_t st) {
+  switch (out_dtype) {
+    case RAGB_F16: return norm_pack_launch<Tin, __half>(in, n, dim, ld_in, out, ld_out, norms, st);
+    case RAGB_BF16: return norm_pack_launch<Tin, __nv_bfloat16>(in, n, dim, ld_in, out, ld_out, norms, st);
+    case RAGB_F32: return norm_pack_launch<Tin, float>(in, n, dim, ld_in, out, ld_out, norms, st);
+  }
+  return fail(RAGB_EINVAL, "bad out dtype %d", out_dtype);
+}
+static int norm_pack_any(const void* in, int in_dtype, int64_t n, int dim, int64_t ld_in, void* out,
+                         int out_dtype, int64_t ld_out, float* norms, cudaStream_t st) {
+  if (n == 0) return RAGB_OK;
+  if (n < 0 || n > (int64_t)8 * 0x7fffffff) return fail(RAGB_EINVAL, "bad row count %lld", (long long)n);
+  if (ld_in < dim) return fail(RAGB_EINVAL, "ld_in %lld < dim %d", (long long)ld_in, dim);
+  if (ld_out % 8 != 0 || ld_out < dim || (uintptr_t)out % 16 != 0)
+    return fail(RAGB_EINVAL, "packed rows need a 16-byte aligned base and ld %% 8 == 0 (ld_out=%lld)", (long long)ld_out);
+  switch (in_dtype) {
+    case RAGB_F16: return norm_pack_out<__half>(in, n, dim, ld_in, out, out_dtype, ld_out, norms, st);
+    case RAGB_BF16: return norm_pack_out<__nv_bfloat16>(in, n, dim, ld_in, out, out_dtype, ld_out, norms, st);
+    case RAGB_F32: return norm_pack_out<float>(in, n, dim, ld_in, out, out_dtype, ld_out, norms, st);
+  }
+  return fail(RAGB_EINVAL, "bad in dtype %d", in_dtype);
+}
+
+template <typename Tin, typename Tm, typename Tout>
+static int pool_launch(const void* tok, const void* mask, int64_t batch, int seq, int hidden, void* out,
+                       int64_t ld_out, float* norms, cudaStream_t st) {
+  const bool vec_ok = ((uintptr_t)tok % 16 == 0) && (((size_t)hidden * sizeof(Tin)) % 16 == 0);
+  const int chunks = (hidden + 7) / 8;
+  const int W = chunks < kPoolThreads ? chunks : kPoolThreads;
+  const int groups = kPoolThreads / W;
+  const size_t smem = sizeof(float) * (((size_t)seq + 3) / 4 * 4 + (size_t)groups * W * 8 + (size_t)chunks * 8 + 8);
+  auto kern = pool_norm_pack_kernel<Tin, Tm, Tout>;
+  if (smem > 48 * 1024) {
+    if (smem > 200 * 1024) return fail(RAGB_EUNSUPPORTED, "seq %d x hidden %d needs %zu B of shared memory", seq, hidden, smem);
+    CU_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  }
+  kern<<<(unsigned)batch, kPoolThreads, smem, st>>>((const Tin*)tok, (const Tm*)mask, seq, hidden, (Tout*)out, ld_out, norms, vec_ok);
+  LAUNCHED();
+  return RAGB_OK;
+}
+template <typename Tin, typename Tm>
+static int pool_out(const void* tok, const void* mask, int64_t batch, int seq, int hidden, void* out,
+                    int out_dtype, int64_t ld_out, float* norms, cudaStream_t st) {
+  switch (out_dtype) {
+    case RAGB_F16: return pool_launch<Tin, Tm, __half>(tok, mask, batch, seq, hidden, out, ld_out, norms, st);
+    case RAGB_BF16: return pool_launch<Tin, Tm, __nv_bfloat16>(tok, mask, batch, seq, hidden, out, ld_out, norms, st);
+    case RAGB_F32: return pool_launch<Tin, Tm, float>(tok, mask, batch, seq, hidden, out, ld_out, norms, st);
+  }
+  return fail(RAGB_EINVAL, "bad out dtype %d", out_dtype);
+}
+template <typename Tin>
+static int pool_mask(const void* tok, const void* mask, int mask_dtype, int64_t batch, int seq, int hidden,
+                     void* out, int out_dtype, int64_t ld_out, float* norms, cudaStream_t st) {
+  switch (mask_dtype) {
+    case RAGB_MASK_U8: return pool_out<Tin, uint8_t>(tok, mask, batch, seq, hidden, out, out_dtype, ld_out, norms, st);
+    case RAGB_MASK_I32: return pool_out<Tin, int32_t>(tok, mask, batch, seq, hidden, out, out_dtype, ld_out, norms, st);
+    case RAGB_MASK_I64: return pool_out<Tin, int64_t>(tok, mask, batch, seq, hidden, out, out_dtype, ld_out, norms, st);
+    case RAGB_MASK_F32: return pool_out<Tin, float>(tok, mask, batch, seq, hidden, out, out_dtype, ld_out, norms, st);
+  }
+  return fail(RAGB_EINVAL, "bad mask dtype %d", mask_dtype);
+}
+static size_t mask_size(int mask_dtype) {
+  return mask_dtype == RAGB_MASK_U8 ? 1 : mask_dtype == RAGB_MASK_I64 ? 8 : 4;
+}
+static int pool_any(const void* tok, int tok_dtype, const void* mask, int mask_dtype, int64_t batch, int seq,
+                    int hidden, void* out, int out_dtype, int64_t ld_out, float* norms, cudaStream_t st) {
+  if (batch == 0) return RAGB_OK;
+  if (batch < 0 || batch > 0x7fffffff) return fail(RAGB_EINVAL, "bad batch %lld", (long long)batch);
+  if (seq <= 0 || hidden <= 0) return fail(RAGB_EINVAL, "bad seq %d / hidden %d", seq, hidden);
+  if (ld_out % 8 != 0 || ld_out < hidden || (uintptr_t)out % 16 != 0)
+    return fail(RAGB_EINVAL, "packed rows need a 16-byte aligned base and ld %% 8 == 0 (ld_out=%lld)", (long long)ld_out);
+  switch (tok_dtype) {
+    case RAGB_F16: return pool_mask<__half>(tok, mask, mask_dtype, batch, seq, hidden, out, out_dtype, ld_out, norms, st);
+    case RAGB_BF16: return pool_mask<__nv_bfloat16>(tok, mask, mask_dtype, batch, seq, hidden, out, out_dtype, ld_out, norms, st);
+    case RAGB_F32: return pool_mask<float>(tok, mask, mask_dtype, batch, seq, hidden, out, out_dtype, ld_out, norms, st);
+  }
+  return fail(RAGB_EINVAL, "bad token dtype %d", tok_dtype);
+}
+
+extern "C" int ragb_norm_pack_dev(int device, const void* in, int in_dtype, int64_t n, int dim, int64_t ld_in,
+                                  void* out, int out_dtype, int64_t ld_out, float* out_norms, void* stream) {
+  if (!in || !out) return fail(RAGB_EINVAL, "NULL buffer");
+  ON_DEVICE(device);
+  return norm_pack_any(in, in_dtype, n, dim, ld_in, out, out_dtype, ld_out, out_norms, (cudaStream_t)stream);
+}
+extern "C" int ragb_pool_norm_pack_dev(int device, const void* tok, int tok_dtype, const void* mask, int mask_dtype,
+                                       int64_t batch, int seq, int hidden, void* out, int out_dtype, int64_t ld_out,
+                                       float* out_norms, void* stream) {
+  if (!tok || !out) return fail(RAGB_EINVAL, "NULL buffer");
+  ON_DEVICE(device);
+  return pool_any(tok, tok_dtype, mask, mask_dtype, batch, seq, hidden, out, out_dtype, ld_out, out_norms, (cudaStream_t)stream);
+}
+
+// rows [first, first+n) are reserved under add_mu; published after the kernel has finished
+static int reserve_rows(ragb_store* s, int64_t n, int64_t* first) {
+  const int64_t cur = s->n.load();
+  if (n < 0) return fail(RAGB_EINVAL, "negative row count");
+  if (cur + n > s->capacity)
+    return fail(RAGB_EFULL, "store full: %lld + %lld > capacity %lld (ragb_store_reserve grows it)",
+                (long long)cur, (long long)n, (long long)s->capacity);
+  *first = cur;
+  return RAGB_OK;
+}
+static void* row_ptr(ragb_store* s, int64_t row) { return (char*)s->rows + (size_t)row * s->ld * elem_size(s->dtype); }
+
+extern "C" int ragb_store_add_dev(ragb_store* s, const void* rows, int in_dtype, int64_t n, int64_t ld_in,
+                                  int64_t* out_first_row, void* stream) {
+  if (!s || (!rows && n)) return fail(RAGB_EINVAL, "NULL argument");
+  std::lock_guard<std::mutex> la(s->add_mu);
+  ON_DEVICE(s->device);
+  int64_t first = 0;
+  RB_TRY(reserve_rows(s, n, &first));
+  cudaStream_t st = stream ? (cudaStream_t)stream : s->stream;
+  RB_TRY(norm_pack_any(rows, in_dtype, n, s->dim, ld_in, row_ptr(s, first), s->dtype, s->ld, s->norms + first, st));
+  // the new rows become searchable once the kernel is done (on a caller stream later
+  // searches are ordered behind it; our own stream is synchronised here)
+  if (!stream) CU_TRY(cudaStreamSynchronize(st));
+  s->n.store(first + n, std::memory_order_release);
+  if (out_first_row) *out_first_row = first;
+  return RAGB_OK;
+}
+
+extern "C" int ragb_store_add(ragb_store* s, const float* rows, int64_t n, int64_t* out_first_row) {
+  if (!s || (!rows && n)) return fail(RAGB_EINVAL, "NULL argument");
+  std::lock_guard<std::mutex> la(s->add_mu);
+  ON_DEVICE(s->device);
+  int64_t first = 0;
+  RB_TRY(reserve_rows(s, n, &first));
+  // stream the rows through a device staging buffer in slabs of <= 64 MiB
+  const size_t row_bytes = (size_t)s->dim * 4;
+  const int64_t slab_rows = std::max<int64_t>(1, std::min<int64_t>(n, (int64_t)((64u << 20) / row_bytes)));
+  RB_TRY(grow(&s->stage_dev, &s->stage_dev_bytes, (size_t)slab_rows * row_bytes, false));
+  for (int64_t r0 = 0; r0 < n; r0 += slab_rows) {
+    const int64_t m = std::min(slab_rows, n - r0);
+    CU_TRY(cudaMemcpyAsync(s->stage_dev, rows + (size_t)r0 * s->dim, (size_t)m * row_bytes, cudaMemcpyHostToDevice, s->stream));
+    RB_TRY(norm_pack_any(s->stage_dev, RAGB_F32, m, s->dim, s->dim, row_ptr(s, first + r0), s->dtype, s->ld,
+                         s->norms + first + r0, s->stream));
+  }
+  CU_TRY(cudaStreamSynchronize(s->stream));
+  s->n.store(first + n, std::memory_order_release);
+  if (out_first_row) *out_first_row = first;
+  return RAGB_OK;
+}
+
+extern "C" int ragb_store_set(ragb_store* s, int64_t row, const float* vec) {
+  if (!s || !vec) return fail(RAGB_EINVAL, "NULL argument");
+  std::lock_guard<std::mutex> la(s->add_mu);
+  std::lock_guard<std::mutex> ls(s->search_mu);  // no search reads a half-written row
+  if (row < 0 || row >= s->n.load()) return fail(RAGB_EINVAL, "row %lld out of range", (long long)row);
+  ON_DEVICE(s->device);
+  RB_TRY(grow(&s->stage_dev, &s->stage_dev_bytes, (size_t)s->dim * 4, false));
+  CU_TRY(cudaMemcpyAsync(s->stage_dev, vec, (size_t)s->dim * 4, cudaMemcpyHostToDevice, s->stream));
+  RB_TRY(norm_pack_any(s->stage_dev, RAGB_F32, 1, s->dim, s->dim, row_ptr(s, row), s->dtype, s->ld, s->norms + row, s->stream));
+  CU_TRY(cudaStreamSynchronize(s->stream));
+  return RAGB_OK;
+}
+
+extern "C" int ragb_store_add_pooled_dev(ragb_store* s, const void* tok, int tok_dtype, const void* mask,
+                                         int mask_dtype, int64_t batch, int seq, int hidden,
+                                         int64_t* out_first_row, void* stream) {
+  if (!s || (!tok && batch)) return fail(RAGB_EINVAL, "NULL argument");
+  if (hidden != s->dim) return fail(RAGB_EINVAL, "hidden %d != store dim %d", hidden, s->dim);
+  std::lock_guard<std::mutex> la(s->add_mu);
+  ON_DEVICE(s->device);
+  int64_t first = 0;
+  RB_TRY(reserve_rows(s, batch, &first));
+  cudaStream_t st = stream ? (cudaStream_t)stream : s->stream;
+  RB_TRY(pool_any(tok, tok_dtype, mask, mask_dtype, batch, seq, hidden, row_ptr(s, first), s->dtype, s->ld, s->norms + first, st));
+  if (!stream) CU_TRY(cudaStreamSynchronize(st));
+  s->n.store(first + batch, std::memory_order_release);
+  if (out_first_row) *out_first_row = first;
+  return RAGB_OK;
+}
+
+extern "C" int ragb_store_add_pooled(ragb_store* s, const void* tok, int tok_dtype, const void* mask, int mask_dtype,
+                                     int64_t batch, int seq, int hidden, int64_t* out_first_row) {
+  if (!s || (!tok && batch)) return fail(RAGB_EINVAL, "NULL argument");
+  if (hidden != s->dim) return fail(RAGB_EINVAL, "hidden %d != store dim %d", hidden, s->dim);
+  if (seq <= 0) return fail(RAGB_EINVAL, "bad seq %d", seq);
+  std::lock_guard<std::mutex> la(s->add_mu);
+  ON_DEVICE(s->device);
+  int64_t first = 0;
+  RB_TRY(reserve_rows(s, batch, &first));
+  const size_t tok_b = (size_t)seq * hidden * elem_size(tok_dtype);
+  const size_t mask_b = mask ? (size_t)seq * mask_size(mask_dtype) : 0;
+  const size_t mask_b_al = (mask_b + 15) / 16 * 16;
+  const int64_t slab = std::max<int64_t>(1, std::min<int64_t>(batch, (int64_t)((128u << 20) / (tok_b + mask_b_al))));
+  const size_t tok_slab = ((size_t)slab * tok_b + 15) / 16 * 16;
+  RB_TRY(grow(&s->stage_dev, &s->stage_dev_bytes, tok_slab + (size_t)slab * mask_b_al + 16, false));
+  char* dtok = (char*)s->stage_dev;
+  char* dmask = dtok + tok_slab;
+  for (int64_t b0 = 0; b0 < batch; b0 += slab) {
+    const int64_t m = std::min(slab, batch - b0);
+    CU_TRY(cudaMemcpyAsync(dtok, (const char*)tok + (size_t)b0 * tok_b, (size_t)m * tok_b, cudaMemcpyHostToDevice, s->stream));
+    if (mask) CU_TRY(cudaMemcpyAsync(dmask, (const char*)mask + (size_t)b0 * mask_b, (size_t)m * mask_b, cudaMemcpyHostToDevice, s->stream));
+    RB_TRY(pool_any(dtok, tok_dtype, mask ? dmask : nullptr, mask_dtype, m, seq, hidden, row_ptr(s, first + b0), s->dtype,
+                    s->ld, s->norms + first + b0, s->stream));
+  }
+  CU_TRY(cudaStreamSynchronize(s->stream));
+  s->n.store(first + batch, std::memory_order_release);
+  if (out_first_row) *out_first_row = first;
+  return RAGB_OK;
+}
+
+extern "C" int ragb_store_get_rows(ragb_store* s, int64_t row0, int64_t n, void* out_rows, float* out_norms) {
+  if (!s) return fail(RAGB_EINVAL, "store is NULL");
+  if (row0 < 0 || n < 0 || row0 + n > s->n.load()) return fail(RAGB_EINVAL, "rows [%lld,%lld) out of range", (long long)row0, (long long)(row0 + n));
+  if (n == 0) return RAGB_OK;
+  std::lock_guard<std::mutex> ls(s->search_mu);
+  ON_DEVICE(s->device);
+  const size_t es = elem_size(s->dtype);
+  if (out_rows)
+    CU_TRY(cudaMemcpy2DAsync(out_rows, (size_t)s->dim * es, row_ptr(s, row0), (size_t)s->ld * es, (size_t)s->dim * es,
+                             (size_t)n, cudaMemcpyDeviceToHost, s->stream));
+  if (out_norms) CU_TRY(cudaMemcpyAsync(out_norms, s->norms + row0, (size_t)n * 4, cudaMemcpyDeviceToHost, s->stream));
+  CU_TRY(cudaStreamSynchronize(s->stream));
+  return RAGB_OK;
+}
+
+// ---------------------------------------------------------------------------
+// search: K3 scan (+K5 merge) dispatch
+// ---------------------------------------------------------------------------
+static constexpr int scan_unroll(int cpl) { return cpl <= 1 ? 8 : cpl == 2 ? 6 : cpl == 3 ? 4 : cpl == 4 ? 3 : 2; }
+
+template <typename T, int G, int CPL>
+static int scan_launch_one(const ScanParams& p, int64_t nq, int n_sm, cudaStream_t st, int* n_lists) {
+  constexpr int U = scan_unroll(CPL);
+  constexpr int R = (32 / G) * U;
+  const int64_t units = (p.row_end - p.row_begin + R - 1) / R;
+  int P = (int)std::min<int64_t>((units + kScanWarps - 1) / kScanWarps, 2 * (int64_t)n_sm);
+  if (P < 1) P = 1;
+  *n_lists = P;
+  if (!p.out) return RAGB_OK;  // sizing pass
+  const size_t smem = (size_t)kScanWarps * listbuf_len(p.kpad) * sizeof(uint64_t);
+  auto kern = scan_topk_kernel<T, G, CPL, U>;
+  if (smem > 48 * 1024) CU_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  kern<<<dim3(P, (unsigned)nq), kScanThreads, smem, st>>>(p);
+  LAUNCHED();
+  return RAGB_OK;
+}
+template <typename T>
+static int scan_launch_generic(const ScanParams& p, int64_t nq, int n_sm, cudaStream_t st, int* n_lists) {
+  constexpr int U = 4;
+  const int64_t units = (p.row_end - p.row_begin + U - 1) / U;
+  int P = (int)std::min<int64_t>((units + kScanWarps - 1) / kScanWarps, 2 * (int64_t)n_sm);
+  if (P < 1) P = 1;
+  *n_lists = P;
+  if (!p.out) return RAGB_OK;
+  const size_t smem = (size_t)kScanWarps * listbuf_len(p.kpad) * sizeof(uint64_t) + (size_t)p.ld * sizeof(float);
+  if (smem > 220 * 1024) return fail(RAGB_EUNSUPPORTED, "k=%d with dim=%d needs %zu B of shared memory", p.k, p.dim, smem);
+  auto kern = scan_topk_generic_kernel<T, U>;
+  if (smem > 48 * 1024) CU_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  kern<<<dim3(P, (unsigned)nq), kScanThreads, smem, st>>>(p);
+  LAUNCHED();
+  return RAGB_OK;
+}
+
+template <typename T, int G>
+static int scan_launch_g(int cpl, const ScanParams& p, int64_t nq, int n_sm, cudaStream_t st, int* nl) {
+  switch (cpl) {
+    case 1: return scan_launch_one<T, G, 1>(p, nq, n_sm, st, nl);
+    case 2: return scan_launch_one<T, G, 2>(p, nq, n_sm, st, nl);
+    case 3: return scan_launch_one<T, G, 3>(p, nq, n_sm, st, nl);
+    case 4: return scan_launch_one<T, G, 4>(p, nq, n_sm, st, nl);
+    case 6: return scan_launch_one<T, G, 6>(p, nq, n_sm, st, nl);
+    case 8: return scan_launch_one<T, G, 8>(p, nq, n_sm, st, nl);
+  }
+  return fail(RAGB_EINVAL, "internal: bad cpl %d", cpl);
+}
+static bool cpl_ok(int c) { return c == 1 || c == 2 || c == 3 || c == 4 || c == 6 || c == 8; }
+
+template <typename T>
+static int scan_launch_t(const ScanParams& p, int64_t nq, int n_sm, cudaStream_t st, int* nl) {
+  const int chunks = (int)(p.ld * sizeof(T) / 16);
+  int bestG = 0;
+  for (int pass = 0; pass < 2 && !bestG; ++pass)
+    for (int G = 32; G >= 8; G >>= 1)
+      if (chunks % G == 0 && cpl_ok(chunks / G) && (pass == 1 || chunks / G >= 2)) { bestG = G; break; }
+  switch (bestG) {
+    case 32: return scan_launch_g<T, 32>(chunks / 32, p, nq, n_sm, st, nl);
+    case 16: return scan_launch_g<T, 16>(chunks / 16, p, nq, n_sm, st, nl);
+    case 8: return scan_launch_g<T, 8>(chunks / 8, p, nq, n_sm, st, nl);
+  }
+  return scan_launch_generic<T>(p, nq, n_sm, st, nl);
+}
+static int scan_launch(int dtype, const ScanParams& p, int64_t nq, int n_sm, cudaStream_t st, int* nl) {
+  switch (dtype) {
+    case RAGB_F16: return scan_launch_t<__half>(p, nq, n_sm, st, nl);
+    case RAGB_BF16: return scan_launch_t<__nv_bfloat16>(p, nq, n_sm, st, nl);
+    case RAGB_F32: return scan_launch_t<float>(p, nq, n_sm, st, nl);
+  }
+  return fail(RAGB_EINVAL, "bad dtype %d", dtype);
+}
+
+static int merge_launch(const uint64_t* keys, int64_t nq, int n_lists, int kpad, int64_t stride_q, int64_t stride_p,
+                        int k, float* out_scores, int64_t* out_ids, uint64_t* out_keys, cudaStream_t st) {
+  if (nq == 0) return RAGB_OK;
+  MergeParams m;
+  m.keys = keys; m.n_lists = n_lists; m.kpad = kpad; m.k = k; m.stride_q = stride_q; m.stride_p = stride_p;
+  m.out_scores = out_scores; m.out_ids = out_ids; m.out_keys = out_keys;
+  const size_t smem = (size_t)kMergeWarps * listbuf_len(kpad) * sizeof(uint64_t);
+  if (smem > 48 * 1024) CU_TRY(cudaFuncSetAttribute(merge_topk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  merge_topk_kernel<<<(unsigned)nq, kMergeThreads, smem, st>>>(m);
+  LAUNCHED();
+  return RAGB_OK;
+}
+
+static int check_search_args(ragb_store* s, const void* q, int64_t nq, int k, int metric, int64_t* rb, int64_t* re) {
+  if (!s) return fail(RAGB_EINVAL, "store is NULL");
+  if (nq < 0 || nq > 65535 * 16) return fail(RAGB_EINVAL, "nq %lld out of range", (long long)nq);
+  if (nq && !q) return fail(RAGB_EINVAL, "q is NULL");
+  if (k <= 0 || k > 1024) return fail(RAGB_EUNSUPPORTED, "k=%d outside [1,1024]", k);
+  if (metric != RAGB_IP && metric != RAGB_COSINE) return fail(RAGB_EINVAL, "bad metric %d", metric);
+  const int64_t n = s->n.load(std::memory_order_acquire);
+  if (*re < 0 || *re > n) *re = n;
+  if (*rb < 0) *rb = 0;
+  if (*rb > *re) *rb = *re;
+  return RAGB_OK;
+}
+
+// core: device pointers, caller holds search_mu and has selected the device.
+// Writes sorted keys (out_keys, kpad per query) and/or decoded (out_scores, out_ids).
+static int search_core(ragb_store* s, const float* q, int64_t nq, int k, int metric, float threshold, int flags,
+                       int64_t rb, int64_t re, const uint8_t* valid, uint32_t id_base, uint64_t* out_keys,
+                       float* out_scores, int64_t* out_ids, cudaStream_t st) {
+  if (nq == 0) return RAGB_OK;
+  const int kpad = kpad_of(k);
+  if (re - rb <= 0)  // empty store / empty window: RAGResult([], []) (:517-521)
+    return merge_launch(nullptr, nq, 0, kpad, 0, 0, k, out_scores, out_ids, out_keys, st);
+  ScanParams p;
+  p.X = s->rows; p.ld = s->ld; p.dim = s->dim; p.row_begin = rb; p.row_end = re; p.valid = valid;
+  p.q = q; p.ld_q = s->dim; p.metric = metric; p.flags = flags; p.threshold = threshold;
+  p.k = k; p.kpad = kpad; p.id_base = id_base; p.out = nullptr;
+  // the grid y dimension caps one launch at 65535 queries
+  int n_lists = 0;
+  RB_TRY(scan_launch(s->dtype, p, nq, s->n_sm, st, &n_lists));  // sizing
+  const int64_t q_step = 65535;
+  RB_TRY(grow(&s->ws, &s->ws_bytes, (size_t)std::min(nq, q_step) * n_lists * kpad * sizeof(uint64_t), false));
+  for (int64_t q0 = 0; q0 < nq; q0 += q_step) {
+    const int64_t m = std::min(q_step, nq - q0);
+    p.q = q + (size_t)q0 * s->dim;
+    p.out = (uint64_t*)s->ws;
+    RB_TRY(scan_launch(s->dtype, p, m, s->n_sm, st, &n_lists));
+    RB_TRY(merge_launch((const uint64_t*)s->ws, m, n_lists, kpad, (int64_t)n_lists * kpad, kpad, k,
+                        out_scores ? out_scores + q0 * k : nullptr, out_ids ? out_ids + q0 * k : nullptr,
+                        out_keys ? out_keys + q0 * kpad : nullptr, st));
+  }
+  return RAGB_OK;
+}
+
+extern "C" int ragb_search_keys_dev(ragb_store* s, const float* q, int64_t nq, int k, int metric, float threshold,
+                                    int flags, int64_t row_begin, int64_t row_end, const uint8_t* valid,
+                                    uint32_t id_base, uint64_t* out_keys, void* stream) {
+  RB_TRY(check_search_args(s, q, nq, k, metric, &row_begin, &row_end));
+  if (nq && !out_keys) return fail(RAGB_EINVAL, "out_keys is NULL");
+  std::lock_guard<std::mutex> ls(s->search_mu);
+  ON_DEVICE(s->device);
+  cudaStream_t st = stream ? (cudaStream_t)stream : s->stream;
+  RB_TRY(search_core(s, q, nq, k, metric, threshold, flags, row_begin, row_end, valid, id_base, out_keys, nullptr, nullptr, st));
+  if (!stream) CU_TRY(cudaStreamSynchronize(st));
+  return RAGB_OK;
+}
+
+extern "C" int ragb_search_dev(ragb_store* s, const float* q, int64_t nq, int k, int metric, float threshold, int flags,
+                               int64_t row_begin, int64_t row_end, const uint8_t* valid, float* out_scores,
+                               int64_t* out_ids, void* stream) {
+  RB_TRY(check_search_args(s, q, nq, k, metric, &row_begin, &row_end));
+  if (nq && (!out_scores || !out_ids)) return fail(RAGB_EINVAL, "output buffer is NULL");
+  std::lock_guard<std::mutex> ls(s->search_mu);
+  ON_DEVICE(s->device);
+  cudaStream_t st = stream ? (cudaStream_t)stream : s->stream;
+  RB_TRY(search_core(s, q, nq, k, metric, threshold, flags, row_begin, row_end, valid, 0, nullptr, out_scores, out_ids, st));
+  if (!stream) CU_TRY(cudaStreamSynchronize(st));
+  return RAGB_OK;
+}
+
+extern "C" int ragb_search(ragb_store* s, const float* q, int64_t nq, int k, int metric, float threshold, int flags,
+                           int64_t row_begin, int64_t row_end, const uint8_t* valid, float* out_scores, int64_t* out_ids) {
+  RB_TRY(check_search_args(s, q, nq, k, metric, &row_begin, &row_end));
+  if (nq && (!out_scores || !out_ids)) return fail(RAGB_EINVAL, "output buffer is NULL");
+  if (nq == 0) return RAGB_OK;
+  std::lock_guard<std::mutex> ls(s->search_mu);
+  ON_DEVICE(s->device);
+  // per-call device buffer: q | scores | ids | valid ; pinned mirror of the first three
+  const size_t qb = (size_t)nq * s->dim * 4, sb = (size_t)nq * k * 4, ib = (size_t)nq * k * 8;
+  const size_t vb = valid ? (size_t)row_end : 0;
+  auto al = [](size_t x) { return (x + 255) / 256 * 256; };
+  const size_t o_s = al(qb), o_i = o_s + al(sb), o_v = o_i + al(ib);
+  RB_TRY(grow(&s->io, &s->io_bytes, o_v + al(vb), false));
+  RB_TRY(grow(&s->pin, &s->pin_bytes, o_v, true));
+  char* d = (char*)s->io;
+  char* h = (char*)s->pin;
+  memcpy(h, q, qb);
+  CU_TRY(cudaMemcpyAsync(d, h, qb, cudaMemcpyHostToDevice, s->stream));
+  if (valid) CU_TRY(cudaMemcpyAsync(d + o_v, valid, vb, cudaMemcpyHostToDevice, s->stream));
+  RB_TRY(search_core(s, (const float*)d, nq, k, metric, threshold, flags, row_begin, row_end,
+                     valid ? (const uint8_t*)(d + o_v) : nullptr, 0, nullptr, (float*)(d + o_s), (int64_t*)(d + o_i), s->stream));
+  CU_TRY(cudaMemcpyAsync(h + o_s, d + o_s, o_v - o_s, cudaMemcpyDeviceToHost, s->stream));
+  CU_TRY(cudaStreamSynchronize(s->stream));
+  memcpy(out_scores, h + o_s, sb);
+  memcpy(out_ids, h + o_i, ib);
+  return RAGB_OK;
+}
+
+extern "C" int ragb_merge_keys_dev(int device, const uint64_t* keys, int64_t nq, int n_lists, int kpad, int64_t stride_q,
+                                   int64_t stride_p, int k, float* out_scores, int64_t* out_ids, void* stream) {
+  if (nq < 0 || n_lists < 0 || k <= 0 || k > 1024) return fail(RAGB_EINVAL, "bad merge arguments");
+  if (kpad != kpad_of(kpad) || kpad < k) return fail(RAGB_EINVAL, "kpad %d must be a power of two >= max(k,16)", kpad);
+  if (nq && n_lists && !keys) return fail(RAGB_EINVAL, "keys is NULL");
+  ON_DEVICE(device);
+  return merge_launch(keys, nq, n_lists, kpad, stride_q, stride_p, k, out_scores, out_ids, nullptr, (cudaStream_t)stream);
+}

@@ -1,0 +1,252 @@
+"""DeviceStore — the device-resident embedding store behind the C ABI.
+
+Thin object wrapper over ``include/ragb200.h``: rows live on one B200 as a row-major
+fp16 / bf16 / fp32 matrix of unit vectors plus the fp32 norm each row had before
+normalising.  This is the slot the reference fills with ``faiss.IndexFlatIP``
+(/root/reference/ollama_rag_system.py:298-305, :372-386) and never searches; here
+``search`` is the exact scan of ``_search_sqlite`` (:480-515).
+
+Host API: numpy arrays in, numpy arrays out.  ``*_dev`` methods take torch CUDA
+tensors (only their ``data_ptr()`` crosses the ABI) and run on torch's current stream.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional, Tuple
+
+import numpy as np
+
+from . import _lib
+from ._lib import BF16, CLAMP01, COSINE, F16, F32, IP, check, lib
+
+_DTYPES = {"fp16": F16, "float16": F16, "half": F16, "bf16": BF16, "bfloat16": BF16, "fp32": F32, "float32": F32}
+_METRICS = {"ip": IP, "inner_product": IP, "cosine": COSINE}
+_NP_MASK = {np.dtype(np.uint8): 0, np.dtype(np.bool_): 0, np.dtype(np.int32): 1, np.dtype(np.int64): 2,
+            np.dtype(np.float32): 3}
+NEG_INF = float("-inf")
+
+
+def _np_elem(dtype_code: int):
+    return {F16: np.float16, BF16: np.uint16, F32: np.float32}[dtype_code]
+
+
+def _tok_code(arr) -> int:
+    """Element code of a host token array; bf16 travels as uint16 bit patterns."""
+    dt = np.dtype(arr.dtype)
+    if dt == np.float16:
+        return F16
+    if dt == np.float32:
+        return F32
+    if dt == np.uint16:
+        return BF16
+    raise TypeError(f"token embeddings must be float16, float32 or uint16(bf16 bits), got {dt}")
+
+
+def _torch_code(t) -> int:
+    import torch
+    return {torch.float16: F16, torch.bfloat16: BF16, torch.float32: F32}[t.dtype]
+
+
+def _torch_mask_code(t) -> int:
+    import torch
+    return {torch.uint8: 0, torch.bool: 0, torch.int32: 1, torch.int64: 2, torch.float32: 3}[t.dtype]
+
+
+def _cur_stream(device_index: int) -> int:
+    import torch
+    return torch.cuda.current_stream(device_index).cuda_stream
+
+
+class DeviceStore:
+    """Fixed-``dim`` store of unit rows on one GPU."""
+
+    def __init__(self, dim: int, dtype: str = "fp16", capacity: int = 1 << 16, device: int = 0):
+        self._h = C.c_void_p()
+        self._lib = lib()
+        code = _DTYPES[dtype] if isinstance(dtype, str) else int(dtype)
+        check(self._lib.ragb_store_create(int(device), int(dim), code, int(capacity), C.byref(self._h)))
+        self.dim, self.dtype_code, self.device = int(dim), code, int(device)
+
+    # -- life cycle ---------------------------------------------------------- #
+    def close(self) -> None:
+        if getattr(self, "_h", None) is not None and self._h.value:
+            self._lib.ragb_store_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __len__(self) -> int:
+        return int(self._lib.ragb_store_size(self._h))
+
+    @property
+    def capacity(self) -> int:
+        return int(self._lib.ragb_store_capacity(self._h))
+
+    @property
+    def ld(self) -> int:
+        return int(self._lib.ragb_store_ld(self._h))
+
+    @property
+    def dtype(self) -> str:
+        return {F16: "fp16", BF16: "bf16", F32: "fp32"}[self.dtype_code]
+
+    def reserve(self, capacity: int) -> None:
+        check(self._lib.ragb_store_reserve(self._h, int(capacity)))
+
+    def clear(self) -> None:
+        check(self._lib.ragb_store_clear(self._h))
+
+    def _room(self, n: int) -> None:
+        need = len(self) + n
+        if need > self.capacity:
+            self.reserve(max(need, 2 * self.capacity, 1024))
+
+    # -- ingest ----------------------------------------------------------------- #
+    def add(self, rows: np.ndarray) -> int:
+        """Normalise + pack fp32 host rows (ollama_rag_system.py:379-383); returns the first row id."""
+        rows = np.ascontiguousarray(np.atleast_2d(rows), dtype=np.float32)
+        if rows.shape[1] != self.dim:
+            raise ValueError(f"rows have dim {rows.shape[1]}, store has {self.dim}")
+        self._room(rows.shape[0])
+        first = C.c_int64(-1)
+        check(self._lib.ragb_store_add(self._h, rows.ctypes.data, rows.shape[0], C.byref(first)))
+        return first.value
+
+    def set(self, row: int, vec: np.ndarray) -> None:
+        """Replace one row in place (INSERT OR REPLACE, :351)."""
+        vec = np.ascontiguousarray(vec, dtype=np.float32).reshape(-1)
+        if vec.shape[0] != self.dim:
+            raise ValueError("dimension mismatch")
+        check(self._lib.ragb_store_set(self._h, int(row), vec.ctypes.data))
+
+    def add_dev(self, rows) -> int:
+        """torch CUDA tensor [n, dim] (fp16/bf16/fp32, row stride allowed) -> normalise + pack."""
+        if rows.dim() != 2 or rows.shape[1] != self.dim or rows.stride(1) != 1:
+            raise ValueError("expected a [n, dim] tensor with unit inner stride")
+        self._room(rows.shape[0])
+        first = C.c_int64(-1)
+        check(self._lib.ragb_store_add_dev(self._h, rows.data_ptr(), _torch_code(rows), rows.shape[0], rows.stride(0),
+                                           C.byref(first), _cur_stream(self.device)))
+        return first.value
+
+    def add_pooled(self, tok: np.ndarray, mask: Optional[np.ndarray]) -> int:
+        """Masked mean-pool + L2-normalise + pack host encoder outputs [B,S,H] (embedding_pipeline.py:424)."""
+        tok = np.ascontiguousarray(tok)
+        if tok.ndim != 3 or tok.shape[2] != self.dim:
+            raise ValueError(f"token embeddings must be [B,S,{self.dim}]")
+        B, S, H = tok.shape
+        mp, mc = None, 0
+        if mask is not None:
+            mask = np.ascontiguousarray(mask)
+            if mask.shape != (B, S):
+                raise ValueError("mask must be [B,S]")
+            if mask.dtype not in _NP_MASK:
+                mask = mask.astype(np.float32)
+            mp, mc = mask.ctypes.data, _NP_MASK[np.dtype(mask.dtype)]
+        self._room(B)
+        first = C.c_int64(-1)
+        check(self._lib.ragb_store_add_pooled(self._h, tok.ctypes.data, _tok_code(tok), mp, mc, B, S, H, C.byref(first)))
+        return first.value
+
+    def add_pooled_dev(self, tok, mask) -> int:
+        """torch CUDA tensors: tok [B,S,H] contiguous, mask [B,S] contiguous or None."""
+        if tok.dim() != 3 or tok.shape[2] != self.dim or not tok.is_contiguous():
+            raise ValueError(f"token embeddings must be contiguous [B,S,{self.dim}]")
+        B, S, H = tok.shape
+        mp, mc = None, 0
+        if mask is not None:
+            if tuple(mask.shape) != (B, S) or not mask.is_contiguous():
+                raise ValueError("mask must be contiguous [B,S]")
+            mp, mc = mask.data_ptr(), _torch_mask_code(mask)
+        self._room(B)
+        first = C.c_int64(-1)
+        check(self._lib.ragb_store_add_pooled_dev(self._h, tok.data_ptr(), _torch_code(tok), mp, mc, B, S, H,
+                                                  C.byref(first), _cur_stream(self.device)))
+        return first.value
+
+    def get_rows(self, row0: int = 0, n: Optional[int] = None) -> Tuple[np.ndarray, np.ndarray]:
+        """Packed rows (float16 / uint16 bf16 bits / float32) and their pre-normalisation norms."""
+        n = len(self) - row0 if n is None else n
+        rows = np.empty((n, self.dim), dtype=_np_elem(self.dtype_code))
+        norms = np.empty(n, dtype=np.float32)
+        check(self._lib.ragb_store_get_rows(self._h, int(row0), int(n), rows.ctypes.data, norms.ctypes.data))
+        return rows, norms
+
+    # -- search ----------------------------------------------------------------- #
+    def search(self, q: np.ndarray, k: int, metric: str = "ip", threshold: float = NEG_INF, clamp01: bool = False,
+               row_begin: int = 0, row_end: int = -1, valid: Optional[np.ndarray] = None,
+               flags: int = 0) -> Tuple[np.ndarray, np.ndarray]:
+        """Exact top-k of host queries ``q [nq, dim]`` -> (ids int64 [nq,k], scores float32 [nq,k]).
+
+        Empty slots hold id -1 / score -inf.  A query of the wrong length scores 0.0
+        against every row (ollama_rag_system.py:201-202).
+        """
+        q = np.ascontiguousarray(np.atleast_2d(q), dtype=np.float32)
+        nq = q.shape[0]
+        if q.shape[1] != self.dim:
+            q = np.zeros((nq, self.dim), dtype=np.float32)  # every row scores 0.0
+        ids = np.empty((nq, k), dtype=np.int64)
+        scores = np.empty((nq, k), dtype=np.float32)
+        vp = None
+        if valid is not None:
+            valid = np.ascontiguousarray(valid, dtype=np.uint8)
+            if valid.shape[0] < (len(self) if row_end < 0 else row_end):
+                raise ValueError("valid mask shorter than the row range")
+            vp = valid.ctypes.data
+        fl = int(flags) | (CLAMP01 if clamp01 else 0)
+        check(self._lib.ragb_search(self._h, q.ctypes.data, nq, int(k), _METRICS[metric], float(threshold), fl,
+                                    int(row_begin), int(row_end), vp, scores.ctypes.data, ids.ctypes.data))
+        return ids, scores
+
+    def search_dev(self, q, k: int, metric: str = "ip", threshold: float = NEG_INF, clamp01: bool = False,
+                   row_begin: int = 0, row_end: int = -1, valid=None, flags: int = 0, out=None):
+        """torch CUDA fp32 queries [nq, dim] -> (ids int64 [nq,k], scores fp32 [nq,k]) CUDA tensors."""
+        import torch
+        if q.dtype != torch.float32 or q.dim() != 2 or q.shape[1] != self.dim or not q.is_contiguous():
+            raise ValueError(f"queries must be contiguous fp32 [nq,{self.dim}]")
+        nq = q.shape[0]
+        if out is None:
+            ids = torch.empty((nq, k), dtype=torch.int64, device=q.device)
+            scores = torch.empty((nq, k), dtype=torch.float32, device=q.device)
+        else:
+            ids, scores = out
+        fl = int(flags) | (CLAMP01 if clamp01 else 0)
+        check(self._lib.ragb_search_dev(self._h, q.data_ptr(), nq, int(k), _METRICS[metric], float(threshold), fl,
+                                        int(row_begin), int(row_end), None if valid is None else valid.data_ptr(),
+                                        scores.data_ptr(), ids.data_ptr(), _cur_stream(self.device)))
+        return ids, scores
+
+    def search_keys_dev(self, q, k: int, metric: str = "ip", threshold: float = NEG_INF, clamp01: bool = False,
+                        id_base: int = 0, flags: int = 0, out=None):
+        """Local top-k as sortable keys [nq, kpad] (int64 tensor holding uint64 bits) for the multi-GPU merge."""
+        import torch
+        nq = q.shape[0]
+        kpad = kpad_of(k)
+        keys = out if out is not None else torch.empty((nq, kpad), dtype=torch.int64, device=q.device)
+        fl = int(flags) | (CLAMP01 if clamp01 else 0)
+        check(self._lib.ragb_search_keys_dev(self._h, q.data_ptr(), nq, int(k), _METRICS[metric], float(threshold), fl,
+                                             0, -1, None, int(id_base), keys.data_ptr(), _cur_stream(self.device)))
+        return keys
+
+
+def kpad_of(k: int) -> int:
+    return int(lib().ragb_kpad(int(k)))
+
+
+def merge_keys_dev(keys, k: int, device: int):
+    """keys: int64 CUDA tensor [n_lists, nq, kpad] of sorted key lists -> (ids [nq,k], scores [nq,k])."""
+    import torch
+    n_lists, nq, kpad = keys.shape
+    ids = torch.empty((nq, k), dtype=torch.int64, device=keys.device)
+    scores = torch.empty((nq, k), dtype=torch.float32, device=keys.device)
+    check(lib().ragb_merge_keys_dev(int(device), keys.data_ptr(), nq, n_lists, kpad, kpad, nq * kpad, int(k),
+                                    scores.data_ptr(), ids.data_ptr(), _cur_stream(device)))
+    return ids, scores
+
+
+def launch_count() -> int:
+    return int(lib().ragb_launch_count())

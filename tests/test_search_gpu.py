@@ -1,0 +1,175 @@
+"""GPU parity of the search path through the C ABI against the oracle and the golden fixtures."""
+import numpy as np
+import pytest
+
+from oracle import ref_search
+from helpers import SEARCH_FIXTURES, load, policy_valid
+
+pytestmark = pytest.mark.gpu
+
+TOL = {"fp16": 1e-3, "bf16": 8e-3, "fp32": 2e-5}  # |score - float64 oracle|; 1e-3 is north_star's bar for fp16
+
+
+def _store(X, dtype):
+    from modular_rag_system_b200 import DeviceStore
+    s = DeviceStore(X.shape[1] if X.ndim == 2 and X.shape[1] else 1, dtype, max(len(X), 1))
+    if len(X):
+        s.add(X)
+    return s
+
+
+def _check(ids, sc, X, Q, k, metric, thr, clamp, tol, valid=None):
+    rows = np.arange(len(X)) if valid is None else np.flatnonzero(valid)
+    Xn = X / np.maximum(np.linalg.norm(X.astype(np.float64), axis=1, keepdims=True), 1e-300) if metric == "ip" else X
+    Xs = Xn[rows].astype(np.float64)
+    rid, rsc = ref_search.search_f64(Xs, Q, k, metric, thr, clamp, recency=rows)
+    for i in range(len(Q)):
+        def score_of(a, i=i):
+            pos = np.searchsorted(rows, a)
+            return ref_search.search_f64(Xs[pos], Q[i], len(a), metric, clamp01=clamp, recency=np.arange(len(a)))[1][0][
+                np.argsort(np.argsort(-np.arange(len(a))))] if False else _scores(Xs[pos], Q[i], metric, clamp)
+        want = np.where(rid[i] >= 0, rows[np.maximum(rid[i], 0)], -1)
+        err = ref_search.check_topk(ids[i], sc[i], want, rsc[i], score_of, tol, thr)
+        assert err is None, f"query {i}: {err}"
+    return rid, rsc
+
+
+def _scores(Xs, q, metric, clamp):
+    q = q.astype(np.float64)
+    d = Xs @ q
+    if metric == "cosine":
+        den = np.linalg.norm(Xs, axis=1) * np.linalg.norm(q)
+        d = np.divide(d, den, out=np.zeros_like(d), where=den != 0)
+    if clamp:
+        d = np.clip(d, 0.0, 1.0)
+    return d
+
+
+@pytest.mark.parametrize("dtype", ["fp16", "fp32", "bf16"])
+@pytest.mark.parametrize("name", SEARCH_FIXTURES)
+def test_golden_fixtures(name, dtype):
+    """Same inputs the unmodified reference ran on; ids/sims must match its output within tolerance."""
+    fx = load(name)
+    X, q, k, thr = fx["X"], fx["q"], int(fx["k"]), float(fx["thr"])
+    if "edge_ts" in name:
+        pytest.skip("non-monotone timestamps are adaptor policy: tests/test_rag_store_gpu.py")
+    valid, _ = policy_valid(fx)
+    s = _store(X, dtype)
+    ids, sc = s.search(q, k, "cosine", thr, clamp01=True, valid=valid.astype(np.uint8)) if len(X) else s.search(q, k, "cosine", thr, True)
+    got = ids[0][ids[0] >= 0]
+    ref_rows, ref_sims = fx["ref_rows"], fx["ref_sims"]
+    Xs = X.astype(np.float64)
+    err = ref_search.check_topk(ids[0], sc[0], np.pad(ref_rows, (0, k - len(ref_rows)), constant_values=-1),
+                                np.pad(ref_sims, (0, k - len(ref_sims)), constant_values=-np.inf),
+                                lambda a: _scores(Xs[a], q, "cosine", True), TOL[dtype], thr)
+    assert err is None, err
+    if dtype == "fp32" and "planted" in name:
+        assert got.tolist() == ref_rows.tolist()
+
+
+@pytest.mark.parametrize("dtype,dim", [("fp16", 384), ("fp16", 768), ("bf16", 384), ("fp32", 384), ("fp16", 100),
+                                       ("fp16", 1024), ("fp32", 72), ("fp16", 3072)])
+def test_random_corpus_vs_oracle(dtype, dim):
+    rng = np.random.default_rng(dim)
+    n = 20000 if dim <= 1024 else 3000
+    X = rng.standard_normal((n, dim)).astype(np.float32)
+    Q = rng.standard_normal((3, dim)).astype(np.float32)
+    Q[1] = X[777] + 0.3 * rng.standard_normal(dim).astype(np.float32)
+    s = _store(X, dtype)
+    for metric in ("cosine", "ip"):
+        Qm = Q if metric == "cosine" else Q / np.linalg.norm(Q, axis=1, keepdims=True)
+        ids, sc = s.search(Qm, 10, metric)
+        _check(ids, sc, X, Qm, 10, metric, -np.inf, False, TOL[dtype])
+    assert ids[1][0] == 777
+
+
+@pytest.mark.parametrize("k", [1, 5, 16, 17, 100, 1000])
+def test_k_range(k):
+    rng = np.random.default_rng(k)
+    X = rng.standard_normal((5000, 128)).astype(np.float32)
+    Q = rng.standard_normal((2, 128)).astype(np.float32)
+    s = _store(X, "fp32")
+    ids, sc = s.search(Q, k, "cosine")
+    rid, rsc = _check(ids, sc, X, Q, k, "cosine", -np.inf, False, TOL["fp32"])
+    assert ref_search.recall_at_k(ids, rid) >= 0.999
+
+
+def test_exact_ties_newest_first_and_threshold():
+    d = 64
+    rng = np.random.default_rng(0)
+    X = rng.standard_normal((300, d)).astype(np.float32)
+    q = rng.standard_normal(d).astype(np.float32)
+    for r in (5, 150, 299, 17):
+        X[r] = q
+    X[40] = 0.0
+    X[41] = -q
+    s = _store(X, "fp16")
+    ids, sc = s.search(q, 6, "cosine", 0.0, clamp01=True)
+    assert ids[0][:4].tolist() == [299, 150, 17, 5]
+    assert np.allclose(sc[0][:4], 1.0, atol=1e-3)
+    ids, sc = s.search(q, 6, "cosine", 0.9, clamp01=True)
+    assert ids[0].tolist() == [299, 150, 17, 5, -1, -1] and np.isneginf(sc[0][4:]).all()
+    # zero query: everything scores 0.0, newest rows first (:214-215)
+    ids, sc = s.search(np.zeros(d, np.float32), 3, "cosine", 0.0, clamp01=True)
+    assert ids[0].tolist() == [299, 298, 297] and (sc[0] == 0).all()
+    # wrong-length query scores 0.0 everywhere (:201-202)
+    ids, sc = s.search(np.ones(7, np.float32), 2, "cosine", 0.0, clamp01=True)
+    assert ids[0].tolist() == [299, 298] and (sc[0] == 0).all()
+
+
+def test_empty_store_and_row_window():
+    from modular_rag_system_b200 import DeviceStore
+    s = DeviceStore(32, "fp16", 16)
+    ids, sc = s.search(np.ones(32, np.float32), 5)
+    assert (ids == -1).all() and np.isneginf(sc).all()
+    rng = np.random.default_rng(1)
+    X = rng.standard_normal((1100, 32)).astype(np.float32)
+    q = X[50].copy()
+    s.add(X)
+    assert len(s) == 1100 and s.capacity >= 1100
+    ids, _ = s.search(q, 1, "cosine")
+    assert ids[0][0] == 50
+    ids, _ = s.search(q, 1, "cosine", row_begin=100)
+    assert ids[0][0] != 50 and ids[0][0] >= 100
+    s.set(50, -q)
+    ids, _ = s.search(q, 1, "cosine")
+    assert ids[0][0] != 50
+
+
+def test_many_queries_scan_path():
+    rng = np.random.default_rng(3)
+    X = rng.standard_normal((4096, 384)).astype(np.float32)
+    Q = rng.standard_normal((33, 384)).astype(np.float32)
+    s = _store(X, "fp16")
+    from modular_rag_system_b200._lib import FORCE_SCAN
+    ids, sc = s.search(Q, 10, "cosine", flags=FORCE_SCAN)
+    _check(ids, sc, X, Q, 10, "cosine", -np.inf, False, TOL["fp16"])
+
+
+def test_device_pointer_entry_and_keys_merge():
+    import torch
+    from modular_rag_system_b200 import merge_keys_dev
+    rng = np.random.default_rng(4)
+    X = rng.standard_normal((6000, 128)).astype(np.float32)
+    Q = rng.standard_normal((5, 128)).astype(np.float32)
+    s = _store(X, "fp16")
+    ref_ids, ref_sc = s.search(Q, 10, "cosine")
+    qd = torch.from_numpy(Q).cuda()
+    ids, sc = s.search_dev(qd, 10, "cosine")
+    torch.cuda.synchronize()
+    assert (ids.cpu().numpy() == ref_ids).all() and np.allclose(sc.cpu().numpy(), ref_sc)
+    # two emulated shards: rows [0,3000) and [3000,6000) as separate stores with id bases
+    a, b = _store(X[:3000], "fp16"), _store(X[3000:], "fp16")
+    ka = a.search_keys_dev(qd, 10, "cosine", id_base=0)
+    kb = b.search_keys_dev(qd, 10, "cosine", id_base=3000)
+    mids, msc = merge_keys_dev(torch.stack([ka, kb]), 10, 0)
+    torch.cuda.synchronize()
+    assert (mids.cpu().numpy() == ref_ids).all() and np.allclose(msc.cpu().numpy(), ref_sc)
+
+
+def test_launch_counter_moves():
+    from modular_rag_system_b200 import launch_count
+    before = launch_count()
+    s = _store(np.eye(16, dtype=np.float32), "fp16")
+    s.search(np.ones(16, np.float32), 2)
+    assert launch_count() >= before + 3
