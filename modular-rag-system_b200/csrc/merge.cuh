@@ -14,6 +14,7 @@ constexpr int kMergeWarps = kMergeThreads / 32;
 struct MergeParams {
   const uint64_t* keys;
   int n_lists, kpad, k;
+  int unsorted;         // lists are unordered key bags (0 = empty) instead of sorted runs
   int64_t stride_q, stride_p;
   float* out_scores;    // [nq][k] or null
   int64_t* out_ids;     // [nq][k] or null
@@ -27,7 +28,18 @@ __global__ void __launch_bounds__(kMergeThreads) merge_topk_kernel(const MergePa
   WarpTopK tk;
   tk.init(smem_lists + (size_t)warp * listbuf_len(p.kpad), p.k, p.kpad, lane);
   const uint64_t* base = p.keys + qi * p.stride_q;
-  for (int l = warp; l < p.n_lists; l += kMergeWarps) tk.merge_list(base + (int64_t)l * p.stride_p, lane);
+  for (int l = warp; l < p.n_lists; l += kMergeWarps) {
+    const uint64_t* list = base + (int64_t)l * p.stride_p;
+    if (p.unsorted) {
+      for (int i0 = 0; i0 < p.kpad; i0 += 32) {
+        const uint64_t key = (i0 + lane < p.kpad) ? list[i0 + lane] : 0;
+        tk.push(key > tk.thr, key, lane);
+      }
+    } else {
+      tk.merge_list(list, lane);
+    }
+  }
+  tk.flush(lane);
   __syncthreads();
   for (int s = 1; s < kMergeWarps; s <<= 1) {
     if ((warp & (2 * s - 1)) == 0 && warp + s < kMergeWarps)

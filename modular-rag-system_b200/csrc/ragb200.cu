@@ -519,16 +519,111 @@ static int scan_launch(int dtype, const ScanParams& p, int64_t nq, int n_sm, cud
 }
 
 static int merge_launch(const uint64_t* keys, int64_t nq, int n_lists, int kpad, int64_t stride_q, int64_t stride_p,
-                        int k, float* out_scores, int64_t* out_ids, uint64_t* out_keys, cudaStream_t st) {
+                        int k, float* out_scores, int64_t* out_ids, uint64_t* out_keys, cudaStream_t st,
+                        bool unsorted = false) {
   if (nq == 0) return RAGB_OK;
   MergeParams m;
   m.keys = keys; m.n_lists = n_lists; m.kpad = kpad; m.k = k; m.stride_q = stride_q; m.stride_p = stride_p;
-  m.out_scores = out_scores; m.out_ids = out_ids; m.out_keys = out_keys;
+  m.out_scores = out_scores; m.out_ids = out_ids; m.out_keys = out_keys; m.unsorted = unsorted ? 1 : 0;
   const size_t smem = (size_t)kMergeWarps * listbuf_len(kpad) * sizeof(uint64_t);
   if (smem > 48 * 1024) CU_TRY(cudaFuncSetAttribute(merge_topk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   merge_topk_kernel<<<(unsigned)nq, kMergeThreads, smem, st>>>(m);
   LAUNCHED();
   return RAGB_OK;
+}
+
+
+// ---------------------------------------------------------------------------
+// search: K4 batched tcgen05 path
+// ---------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static int make_map(GemmState* g, CUtensorMap* map, int dtype, const void* base, int dim, int64_t rows, int64_t ld,
+                    int box_rows) {
+  if (!g->encode_fn) {
+    cudaDriverEntryPointQueryResult qres;
+    void* fn = nullptr;
+    CU_TRY(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres));
+    if (!fn || qres != cudaDriverEntryPointSuccess) return fail(RAGB_ECUDA, "cuTensorMapEncodeTiled not available from the driver");
+    g->encode_fn = fn;
+  }
+  cuuint64_t gdim[2] = {(cuuint64_t)dim, (cuuint64_t)rows};
+  cuuint64_t gstride[1] = {(cuuint64_t)ld * 2};
+  cuuint32_t box[2] = {(cuuint32_t)kGemmKB, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = ((EncodeTiledFn)g->encode_fn)(map, dtype == RAGB_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16,
+                                            2, const_cast<void*>(base), gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                                            CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                                            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return fail(RAGB_ECUDA, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+  return RAGB_OK;
+}
+
+static bool gemm_eligible(const ragb_store* s, int64_t nq, int k, int flags) {
+  if (s->dtype == RAGB_F32 || kpad_of(k) > kGemmMaxKpad || (flags & RAGB_FORCE_SCAN)) return false;
+  return (flags & RAGB_FORCE_GEMM) || nq >= 4;
+}
+
+template <typename T>
+static int rescore_launch(ragb_store* s, const float* q, int64_t nq, int metric, int flags, float threshold,
+                          uint32_t id_base, int kpad, uint64_t* keys, cudaStream_t st) {
+  const int64_t warps = nq * kpad;
+  rescore_kernel<T><<<(unsigned)((warps + 7) / 8), 256, 0, st>>>((const T*)s->rows, s->ld, s->dim, q, nq, metric, flags,
+                                                                threshold, id_base, kpad, keys);
+  LAUNCHED();
+  return RAGB_OK;
+}
+
+static int gemm_search(ragb_store* s, const float* q, int64_t nq, int k, int metric, float threshold, int flags,
+                       int64_t rb, int64_t re, const uint8_t* valid, uint32_t id_base, uint64_t* out_keys,
+                       float* out_scores, int64_t* out_ids, cudaStream_t st) {
+  GemmState* g = &s->gemm;
+  const int kpad = kpad_of(k);
+  if (g->map_rows != s->rows || g->map_capacity != s->capacity) {
+    RB_TRY(make_map(g, &g->map_x, s->dtype, s->rows, s->dim, s->capacity, s->ld, kGemmN));
+    g->map_rows = s->rows; g->map_capacity = s->capacity;
+  }
+  const int n_qt = (int)((nq + kGemmM - 1) / kGemmM);
+  const int64_t nq_pad = (int64_t)n_qt * kGemmM;
+  RB_TRY(grow(&g->qh, &g->qh_bytes, (size_t)nq_pad * s->ld * 2, false));
+  if (s->dtype == RAGB_BF16)
+    convert_queries_kernel<__nv_bfloat16><<<(unsigned)(nq_pad / 4), 128, 0, st>>>(q, nq, s->dim, s->ld, metric, (__nv_bfloat16*)g->qh);
+  else
+    convert_queries_kernel<__half><<<(unsigned)(nq_pad / 4), 128, 0, st>>>(q, nq, s->dim, s->ld, metric, (__half*)g->qh);
+  LAUNCHED();
+  CUtensorMap map_q;
+  RB_TRY(make_map(g, &map_q, s->dtype, g->qh, s->dim, nq_pad, s->ld, kGemmM));
+
+  GemmParams p;
+  p.dim = s->dim; p.row_begin = rb; p.row_end = re; p.valid = valid; p.nq = nq; p.n_qt = n_qt;
+  p.n_tiles = (re - rb + kGemmN - 1) / kGemmN;
+  int splits = n_qt >= s->n_sm ? 1 : s->n_sm / n_qt;
+  if (splits > p.n_tiles) splits = (int)p.n_tiles;
+  p.n_splits = splits;
+  p.flags = flags; p.threshold = threshold; p.k = k; p.kpad = kpad; p.stages = 4;
+  p.id_base = id_base; p.idesc = umma_idesc(s->dtype == RAGB_BF16, kGemmM, kGemmN);
+  const size_t part_bytes = (size_t)nq_pad * splits * kpad * sizeof(uint64_t);
+  const size_t tmp_bytes = (size_t)nq * kpad * sizeof(uint64_t);
+  RB_TRY(grow(&s->ws, &s->ws_bytes, part_bytes + tmp_bytes, false));
+  p.out = (uint64_t*)s->ws;
+  uint64_t* tmp = (uint64_t*)((char*)s->ws + part_bytes);
+  const size_t smem = 1024 + (size_t)p.stages * kStageBytes + (size_t)kpad * kGemmM * 8 + (2 * p.stages + 4) * 8 + 16;
+  static bool attr_set = false;
+  if (!attr_set) {
+    CU_TRY(cudaFuncSetAttribute(gemm_topk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448));
+    attr_set = true;
+  }
+  gemm_topk_kernel<<<(unsigned)(n_qt * splits), kGemmThreads, smem, st>>>(map_q, g->map_x, p);
+  LAUNCHED();
+  const bool rescore = !(flags & RAGB_NO_RESCORE);
+  if (!rescore)
+    return merge_launch(p.out, nq, splits, kpad, (int64_t)splits * kpad, kpad, k, out_scores, out_ids, out_keys, st);
+  RB_TRY(merge_launch(p.out, nq, splits, kpad, (int64_t)splits * kpad, kpad, k, nullptr, nullptr, tmp, st));
+  if (s->dtype == RAGB_BF16) RB_TRY(rescore_launch<__nv_bfloat16>(s, q, nq, metric, flags, threshold, id_base, kpad, tmp, st));
+  else RB_TRY(rescore_launch<__half>(s, q, nq, metric, flags, threshold, id_base, kpad, tmp, st));
+  return merge_launch(tmp, nq, 1, kpad, kpad, kpad, k, out_scores, out_ids, out_keys, st, /*unsorted=*/true);
 }
 
 static int check_search_args(ragb_store* s, const void* q, int64_t nq, int k, int metric, int64_t* rb, int64_t* re) {
@@ -553,6 +648,8 @@ static int search_core(ragb_store* s, const float* q, int64_t nq, int k, int met
   const int kpad = kpad_of(k);
   if (re - rb <= 0)  // empty store / empty window: RAGResult([], []) (:517-521)
     return merge_launch(nullptr, nq, 0, kpad, 0, 0, k, out_scores, out_ids, out_keys, st);
+  if (gemm_eligible(s, nq, k, flags))
+    return gemm_search(s, q, nq, k, metric, threshold, flags, rb, re, valid, id_base, out_keys, out_scores, out_ids, st);
   ScanParams p;
   p.X = s->rows; p.ld = s->ld; p.dim = s->dim; p.row_begin = rb; p.row_end = re; p.valid = valid;
   p.q = q; p.ld_q = s->dim; p.metric = metric; p.flags = flags; p.threshold = threshold;
