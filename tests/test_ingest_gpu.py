@@ -25,11 +25,14 @@ ULP = {"fp16": 2.0 ** -11, "bf16": 2.0 ** -8, "fp32": 2.0 ** -23}
 
 def _assert_packed(got, want_f32, dtype):
     """Equal to the oracle's packed value up to one unit in the last place of the packed type
-    (the fp32 norm may differ in its last bit with summation order), and mostly bit-equal."""
+    (the fp32 norm may differ in its last bit with summation order), and mostly bit-equal.
+    For an fp32 store every quotient inherits the norm's last-bit difference, so only the
+    2-ulp bound is asserted there."""
     want = _pack(want_f32, dtype)
     diff = np.abs(got - want)
     assert np.all(diff <= 2 * ULP[dtype] * np.maximum(np.abs(want), 2.0 ** -14)), float(diff.max())
-    assert np.mean(got == want) > 0.98
+    if dtype != "fp32":
+        assert np.mean(got == want) > 0.98
 
 
 @pytest.mark.parametrize("dtype", ["fp16", "bf16", "fp32"])
