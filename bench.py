@@ -1,0 +1,402 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark of the retrieval hot path (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference]
+                    [--workload 10Mx768|1Mx384] [--batch B] [--k 10] [--no-extras]
+
+A "step" is one pass of the search path over one batch of B synthetic queries against the
+whole corpus (exact top-k, inner product over unit rows).  The corpus is random unit vectors
+generated on the device (seed 0), queries seed 1.  With N > 1 (torchrun, one rank per GPU) the
+corpus is row-sharded over the ranks (strong scaling: the total row count is fixed), every
+rank scans its shard, ONE NCCL all-gather moves k candidates per query per rank, and a merge
+kernel finishes on every rank.
+
+Prints ONE JSON line (rank 0).  `value` = queries/s with queries and corpus resident in HBM,
+`e2e` = the same through the host-buffer entry point (H2D of the queries and D2H of ids+scores
+inside the timed region), `roofline` = the dominant kernel against MEASURED_PEAKS.json,
+`cpu_baseline` = the CPU oracle (numpy float64 restatement of the reference's scan) timed on
+this box's host cores on a bounded row sample.  `--impl reference` times only that CPU path.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT))
+
+WORKLOADS = {
+    # BASELINE.json configs[3] shape on one GPU / row-sharded over N GPUs; north_star's target config
+    "10Mx768": dict(n=10_000_000, d=768, dtype="fp16"),
+    # BASELINE.json configs[1]
+    "1Mx384": dict(n=1_000_000, d=384, dtype="fp16"),
+}
+METRIC = "queries/sec exact top-10"
+FALLBACK_PEAKS = {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0}
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="10Mx768", choices=sorted(WORKLOADS))
+    ap.add_argument("--batch", type=int, default=1024)
+    ap.add_argument("--k", type=int, default=10)
+    ap.add_argument("--no-extras", action="store_true", help="skip the secondary cases (batch 1, 1Mx384)")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline leg")
+    ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target CPU time of one baseline sample")
+    return ap.parse_args()
+
+
+def peaks():
+    p = ROOT / "MEASURED_PEAKS.json"
+    if p.exists():
+        try:
+            d = json.loads(p.read_text())
+            return d, "measured (MEASURED_PEAKS.json)"
+        except Exception:
+            pass
+    return dict(FALLBACK_PEAKS), "fallback (B200_PROFILING.md)"
+
+
+# --------------------------------------------------------------------------- #
+# CPU baseline: the oracle (numpy float64 restatement of ollama_rag_system.py:199-222,480-515)
+# --------------------------------------------------------------------------- #
+def cpu_sample(n_total: int, d: int, batch: int, k: int, target_s: float):
+    """Time the CPU oracle on a bounded row sample of the same workload; returns
+    (qps extrapolated linearly to n_total rows, seconds of the sample, rows in the sample, cores)."""
+    import numpy as np
+    from oracle import ref_search
+    cores = len(os.sched_getaffinity(0))
+    rng = np.random.default_rng(0)
+    Q = rng.standard_normal((batch, d)).astype(np.float32)
+
+    def make(n):
+        X = rng.standard_normal((n, d)).astype(np.float32)
+        X /= np.linalg.norm(X, axis=1, keepdims=True)
+        return X.astype(np.float16)
+
+    def run(X):
+        t0 = time.perf_counter()
+        ref_search.search_f64_blocked(X, Q, k, "ip", block_rows=16384)
+        return time.perf_counter() - t0
+
+    n0 = 16384
+    X0 = make(n0)
+    run(X0)  # BLAS warm-up
+    t_cal = run(X0)
+    n_s = int(min(n_total, max(n0, n0 * target_s / max(t_cal, 1e-6))))
+    n_s = max(n0, (n_s // 16384) * 16384)
+    X = make(n_s) if n_s != n0 else X0
+    t = run(X)
+    qps = batch / (t * n_total / n_s)
+    return qps, t, n_s, cores
+
+
+def cpu_baseline_obj(wl, batch, k, target_s):
+    qps, t, n_s, cores = cpu_sample(wl["n"], wl["d"], batch, k, target_s)
+    return {
+        "value": qps, "unit": "queries/s", "cores": cores, "kind": "port",
+        "sample": (f"oracle.search_f64_blocked (numpy float64 GEMM + top-k, all BLAS threads) on {n_s} of "
+                   f"{wl['n']} rows x {wl['d']}, batch {batch}: {t:.2f} s; scaled linearly in rows"),
+    }, t
+
+
+def run_reference(args):
+    """--impl reference: the CPU path only, K bounded samples (rank 0 alone under torchrun)."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    wl = WORKLOADS[args.workload]
+    # keep the whole run within a few minutes: each step is one bounded sample
+    per = min(args.cpu_seconds, 150.0 / max(1, args.steps + args.warmup))
+    vals, secs = [], []
+    for i in range(args.warmup + args.steps):
+        obj, t = cpu_baseline_obj(wl, args.batch, args.k, per)
+        if i >= args.warmup:
+            vals.append(obj["value"]); secs.append(t)
+    qps = sum(vals) / len(vals)
+    obj["value"] = qps
+    line = {
+        "impl": "reference", "metric": METRIC, "value": qps, "unit": "queries/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": 1e3 * args.batch / qps, "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": f"{args.workload} fp16 rows, inner product, top-{args.k}, batch {args.batch}",
+                   "timing": "each step = one bounded row sample, extrapolated linearly to the full corpus"},
+        "cpu_baseline": obj,
+        "e2e": {"value": qps, "unit": "queries/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# --------------------------------------------------------------------------- #
+# clocks during the timed region (B200_PROFILING.md recipe)
+# --------------------------------------------------------------------------- #
+class ClockSampler:
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.proc, self.path = index, None, None
+
+    def __enter__(self):
+        try:
+            f = tempfile.NamedTemporaryFile("w", suffix=".csv", delete=False)
+            self.path = f.name
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100", "-i", str(self.index)], stdout=f, stderr=subprocess.DEVNULL)
+        except Exception:
+            self.proc = None
+        return self
+
+    def __exit__(self, *a):
+        if self.proc is not None:
+            time.sleep(0.15)
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=5)
+            except Exception:
+                self.proc.kill()
+
+    def summary(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        if not self.path or not os.path.exists(self.path):
+            return out
+        sm, mx, reasons = [], [], set()
+        for ln in open(self.path):
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 8:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[4:8]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        os.unlink(self.path)
+        if sm:
+            sm.sort()
+            out.update(sm_mhz=sm[len(sm) // 2], sm_max_mhz=max(mx), reasons=sorted(reasons), samples=len(sm))
+        return out
+
+
+# --------------------------------------------------------------------------- #
+# GPU arm
+# --------------------------------------------------------------------------- #
+def fill_store(pkg, torch, wl, r0, r1, device):
+    """Rows [r0, r1) of the synthetic corpus: N(0,1) rows, normalised and packed by the ingest kernel."""
+    n = r1 - r0
+    store = pkg.DeviceStore(wl["d"], wl["dtype"], max(n, 1), device=device)
+    slab = 500_000
+    for b0 in range(r0, r1, slab):
+        m = min(slab, r1 - b0)
+        g = torch.Generator(device=f"cuda:{device}").manual_seed(1_000_003 * (b0 // slab) + 7)
+        store.add_dev(torch.randn((m, wl["d"]), generator=g, device=f"cuda:{device}"))
+    torch.cuda.synchronize(device)
+    return store
+
+
+def time_device(torch, dist, fn, steps, warmup, world):
+    """W warm-ups, then K steps between barrier+sync, CUDA events on the launching stream; max over ranks (ms)."""
+    for _ in range(warmup):
+        fn()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+        torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    ms = e0.elapsed_time(e1)
+    if world > 1:
+        t = torch.tensor([ms], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    return ms
+
+
+def time_host(torch, dist, fn, steps, warmup, world):
+    """Same protocol for a host-synchronous call (the e2e leg): wall clock between syncs, max over ranks (ms)."""
+    for _ in range(warmup):
+        fn()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        fn()
+    torch.cuda.synchronize()
+    ms = (time.perf_counter() - t0) * 1e3
+    if world > 1:
+        t = torch.tensor([ms], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    return ms
+
+
+def roofline_obj(kind, store, torch, fn, iters, work_per_launch, pk, pk_src, sustained):
+    """Kernel-only time of the dominant kernel from the C ABI's event brackets -> roofline object."""
+    store.profile(True)
+    for _ in range(iters):
+        fn()
+    torch.cuda.synchronize()
+    ms, n = store.profile_read()
+    store.profile(False)
+    per = ms / max(n, 1)
+    if kind == "hbm":
+        achieved = work_per_launch / per / 1e6  # GB/s
+        peak, unit = float(pk["hbm_gbs"]), "GB/s"
+    else:
+        achieved = work_per_launch / per / 1e9  # TFLOP/s
+        peak = float(pk["bf16_tflops_sustained" if sustained else "bf16_tflops"])
+        unit = "TFLOP/s"
+    return {"bound": kind, "achieved": achieved, "peak": peak, "unit": unit, "frac": achieved / peak,
+            "traffic": None, "kernel_ms": per, "launches_timed": n, "peak_source": pk_src +
+            (", sustained" if (kind == "tensor" and sustained) else ", burst" if kind == "tensor" else "")}
+
+
+def run_b200(args):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    import modular_rag_system_b200 as pkg
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus and world > 1:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}")
+    if args.gpus > 1 and world == 1:
+        raise SystemExit("launch N>1 with: python -m torch.distributed.run --nproc-per-node N bench.py --gpus N ...")
+    torch.cuda.set_device(local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    pk, pk_src = peaks()
+    wl = WORKLOADS[args.workload]
+    n, d, B, k = wl["n"], wl["d"], args.batch, args.k
+    bounds = pkg.shard_bounds(n, world)
+    r0, r1 = bounds[rank]
+    store = fill_store(pkg, torch, wl, r0, r1, local)
+    searcher = pkg.ShardedSearcher(store, r0)
+    gq = torch.Generator(device="cuda").manual_seed(1)
+    Q = torch.randn((B, d), generator=gq, device="cuda")
+    Q = (Q / Q.norm(dim=1, keepdim=True)).contiguous()
+    Qh = Q.cpu().numpy()
+    if world > 1:  # warm NCCL up outside every timed region
+        searcher.search_dev(Q, k)
+        torch.cuda.synchronize()
+
+    # ---- device-resident leg (value) ------------------------------------------------
+    step = (lambda: searcher.search_dev(Q, k, "ip"))
+    l0 = pkg.launch_count()
+    with ClockSampler(local) as cs:
+        ms = time_device(torch, dist, step, args.steps, args.warmup, world)
+    launches = (pkg.launch_count() - l0) * args.steps // (args.steps + args.warmup)
+    clocks = cs.summary()
+    qps = B * args.steps / (ms / 1e3)
+
+    # ---- end-to-end leg (host buffers through the public entry point) ---------------
+    if world == 1:
+        e2e_fn = (lambda: store.search(Qh, k, "ip"))          # C ABI ragb_search: H2D + kernels + D2H
+    else:
+        e2e_fn = (lambda: searcher.search(Qh, k, "ip"))
+    ms_e2e = time_host(torch, dist, e2e_fn, args.steps, args.warmup, world)
+    e2e = {"value": B * args.steps / (ms_e2e / 1e3), "unit": "queries/s", "h2d_bytes_per_step": B * d * 4,
+           "d2h_bytes_per_step": B * k * 12, "ms_per_step": ms_e2e / args.steps,
+           "entry": "ragb_search (C ABI, host pointers)" if world == 1 else "ShardedSearcher.search (host arrays)"}
+
+    # ---- roofline of the dominant kernel (this rank's shard), measured live ---------
+    tensor_path = B >= 4
+    work = 2.0 * B * (r1 - r0) * d if tensor_path else float(r1 - r0) * d * 2
+    roof = roofline_obj("tensor" if tensor_path else "hbm", store, torch, step, max(3, min(args.steps, 10)), work,
+                        pk, pk_src, sustained=(ms / args.steps > 50.0))
+    roof["kernel"] = "gemm_topk_kernel (tcgen05)" if tensor_path else "scan_topk_kernel"
+    roof["kernel_share_of_step"] = roof["kernel_ms"] / (ms / args.steps)
+
+    extras = []
+    if rank == 0 and world == 1 and not args.no_extras:
+        extras = run_extras(args, pkg, torch, store, wl, pk, pk_src)
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        cpu, _ = cpu_baseline_obj(wl, B, k, args.cpu_seconds)
+
+    if world > 1:
+        t = torch.tensor([launches], device="cuda", dtype=torch.int64)
+        dist.all_reduce(t)
+        launches = int(t.item())
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": qps, "unit": "queries/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "f16 operands, f32 accumulate", "data": "synthetic",
+            "config": {"workload": f"{args.workload} fp16 unit rows, inner product, exact top-{k}, batch {B}",
+                       "rows_total": n, "dim": d, "batch": B, "k": k,
+                       "parallelism": f"rows sharded over {world} GPU(s), all-gather of k candidates + merge",
+                       "l2": f"corpus shard {(r1 - r0) * d * 2 / 1e6:.0f} MB per GPU vs 126 MB L2: no flush needed"
+                             if (r1 - r0) * d * 2 > 4 * 126e6 else "corpus shard comparable to L2; not flushed"},
+            "e2e": e2e, "roofline": roof, "cpu_baseline": cpu, "gpu_launches": launches, "clocks": clocks,
+            "extras": extras,
+        }
+        print(json.dumps(line), flush=True)
+    store.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def run_extras(args, pkg, torch, store, wl, pk, pk_src):
+    """Secondary cases of the metric on one GPU: batch 1 on the same corpus, and the other named corpus."""
+    out = []
+
+    def case(st, w, name, B):
+        g = torch.Generator(device="cuda").manual_seed(2)
+        Q = torch.randn((B, w["d"]), generator=g, device="cuda")
+        Q = (Q / Q.norm(dim=1, keepdim=True)).contiguous()
+        fn = (lambda: st.search_dev(Q, args.k, "ip"))
+        steps = 50 if B == 1 else args.steps
+        ms = time_device(torch, None, fn, steps, args.warmup, 1)
+        tensor = B >= 4
+        work = 2.0 * B * len(st) * w["d"] if tensor else float(len(st)) * w["d"] * 2
+        roof = roofline_obj("tensor" if tensor else "hbm", st, torch, fn, 10, work, pk, pk_src, sustained=False)
+        out.append({"workload": f"{name} batch {B}", "value": B * steps / (ms / 1e3), "unit": "queries/s",
+                    "ms_per_step": ms / steps, "roofline": roof})
+
+    case(store, wl, args.workload, 1 if args.batch != 1 else 1024)
+    other = "1Mx384" if args.workload != "1Mx384" else None
+    if other:
+        w2 = WORKLOADS[other]
+        st2 = fill_store(pkg, torch, w2, 0, w2["n"], store.device)
+        case(st2, w2, other, 1024)
+        case(st2, w2, other, 1)
+        st2.close()
+    return out
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)
+
+
+if __name__ == "__main__":
+    main()

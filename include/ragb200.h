@@ -124,6 +124,15 @@ int ragb_search_dev(ragb_store* s, const float* q, int64_t nq, int k, int metric
                     int flags, int64_t row_begin, int64_t row_end, const uint8_t* valid,
                     float* out_scores, int64_t* out_ids, void* stream);
 
+/* ---- measurement ------------------------------------------------------------
+ * While enabled, every search call brackets its dominant kernel (the scan for the
+ * bandwidth-bound path, the tcgen05 kernel for the batched path) with CUDA events on the
+ * launching stream.  ragb_store_profile_read waits for them, returns the summed kernel
+ * time and the number of bracketed launches, and resets the counters.  The reference has
+ * only wall-clock retrieval_time (ollama_rag_system.py:390,401). */
+int ragb_store_profile(ragb_store* s, int enable);
+int ragb_store_profile_read(ragb_store* s, double* total_ms, int64_t* n_launches);
+
 /* ---- multi-GPU building blocks (row-sharded corpus, one process per GPU) ----
  * local top-k as sortable 64-bit keys: (ordered score bits << 32) | (row + id_base),
  * kpad = ragb_kpad(k) keys per query, sorted best first, 0 = empty slot.

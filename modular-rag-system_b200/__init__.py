@@ -6,5 +6,7 @@
 """
 from ._lib import RagbError, build, lib  # noqa: F401
 from .store import DeviceStore, kpad_of, launch_count, merge_keys_dev  # noqa: F401
+from .sharded import ShardedSearcher, shard_bounds  # noqa: F401
 
-__all__ = ["DeviceStore", "RagbError", "build", "lib", "kpad_of", "launch_count", "merge_keys_dev"]
+__all__ = ["DeviceStore", "RagbError", "build", "lib", "kpad_of", "launch_count", "merge_keys_dev",
+           "ShardedSearcher", "shard_bounds"]

@@ -50,6 +50,8 @@ SIGNATURES = {
     "ragb_store_get_rows": (_i, [_vp, _i64, _i64, _vp, _vp]),
     "ragb_search": (_i, [_vp, _vp, _i64, _i, _i, _f, _i, _i64, _i64, _vp, _vp, _vp]),
     "ragb_search_dev": (_i, [_vp, _vp, _i64, _i, _i, _f, _i, _i64, _i64, _vp, _vp, _vp, _vp]),
+    "ragb_store_profile": (_i, [_vp, _i]),
+    "ragb_store_profile_read": (_i, [_vp, C.POINTER(C.c_double), _pi64]),
     "ragb_kpad": (_i, [_i]),
     "ragb_search_keys_dev": (_i, [_vp, _vp, _i64, _i, _i, _f, _i, _i64, _i64, _vp, C.c_uint32, _vp, _vp]),
     "ragb_merge_keys_dev": (_i, [_i, _vp, _i64, _i, _i, _i64, _i64, _i, _vp, _vp, _vp]),

@@ -58,6 +58,13 @@ __device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, u
       "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
       : "memory");
 }
+// one lane of a converged warp; the surrounding code stays warp-uniform so that descriptors and
+// addresses live in uniform registers (no per-instruction R2UR/ELECT waterfall around UTCHMMA)
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile("{\n\t.reg .pred P;\n\telect.sync _|P, 0xffffffff;\n\tselp.u32 %0, 1, 0, P;\n\t}" : "=r"(pred));
+  return pred != 0;
+}
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_commit(uint64_t* bar) {
@@ -201,45 +208,48 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constan
 
   if (warp == 0) {
     // ===== TMA producer =====
-    if (lane == 0) {
-      uint32_t it = 0;
-      for (int64_t t = t0; t < t1; ++t) {
-        const int row0 = (int)(p.row_begin + t * kGemmN);
-        for (int kb = 0; kb < n_kb; ++kb, ++it) {
-          const int s = it % p.stages;
-          const uint32_t ph = (it / p.stages) & 1;
-          mbar_wait(&empty_bar[s], ph ^ 1);
+    uint32_t it = 0;
+    for (int64_t t = t0; t < t1; ++t) {
+      const int row0 = (int)(p.row_begin + t * kGemmN);
+      for (int kb = 0; kb < n_kb; ++kb, ++it) {
+        const int s = it % p.stages;
+        const uint32_t ph = (it / p.stages) & 1;
+        mbar_wait(&empty_bar[s], ph ^ 1);
+        if (elect_one()) {
           mbar_expect_tx(&full_bar[s], kStageBytes);
           uint8_t* a = stage_base + (size_t)s * kStageBytes;
           tma_load_2d(a, &map_q, &full_bar[s], kb * kGemmKB, qt * kGemmM);
           tma_load_2d(a + kStageBytesA, &map_x, &full_bar[s], kb * kGemmKB, row0);
         }
+        __syncwarp();
       }
     }
   } else if (warp == 1) {
     // ===== MMA issuer =====
-    if (lane == 0) {
-      uint32_t it = 0, tt = 0;
-      for (int64_t t = t0; t < t1; ++t, ++tt) {
-        const uint32_t acc = tt & 1, aph = (tt >> 1) & 1;
-        mbar_wait(&tempty_bar[acc], aph ^ 1);
+    uint32_t it = 0, tt = 0;
+    for (int64_t t = t0; t < t1; ++t, ++tt) {
+      const uint32_t acc = tt & 1, aph = (tt >> 1) & 1;
+      mbar_wait(&tempty_bar[acc], aph ^ 1);
+      tc_fence_after();
+      const uint32_t d_tmem = tmem_base + acc * kGemmN;
+      for (int kb = 0; kb < n_kb; ++kb, ++it) {
+        const int s = it % p.stages;
+        const uint32_t ph = (it / p.stages) & 1;
+        mbar_wait(&full_bar[s], ph);
         tc_fence_after();
-        const uint32_t d_tmem = tmem_base + acc * kGemmN;
-        for (int kb = 0; kb < n_kb; ++kb, ++it) {
-          const int s = it % p.stages;
-          const uint32_t ph = (it / p.stages) & 1;
-          mbar_wait(&full_bar[s], ph);
-          tc_fence_after();
-          const uint32_t a_addr = smem_u32(stage_base + (size_t)s * kStageBytes);
-          const uint64_t adesc = umma_desc_sw128(a_addr);
-          const uint64_t bdesc = umma_desc_sw128(a_addr + kStageBytesA);
+        const uint32_t a_addr = smem_u32(stage_base + (size_t)s * kStageBytes);
+        const uint64_t adesc = umma_desc_sw128(a_addr);
+        const uint64_t bdesc = umma_desc_sw128(a_addr + kStageBytesA);
+        if (elect_one()) {
 #pragma unroll
           for (int k4 = 0; k4 < kGemmKB / 16; ++k4)  // +32 bytes per K=16 step inside the swizzle row
             tc_mma_f16(d_tmem, adesc + (uint64_t)(k4 * 2), bdesc + (uint64_t)(k4 * 2), p.idesc, (kb | k4) != 0);
           tc_commit(&empty_bar[s]);  // frees the stage when these MMAs have read it
         }
-        tc_commit(&tfull_bar[acc]);  // accumulator complete
+        __syncwarp();
       }
+      if (elect_one()) tc_commit(&tfull_bar[acc]);  // accumulator complete
+      __syncwarp();
     }
   } else {
     // ===== epilogue: thread == query =====
@@ -341,10 +351,18 @@ struct GemmState {
   void* qh = nullptr;              // converted queries
   size_t qh_bytes = 0;
   void* encode_fn = nullptr;       // cuTensorMapEncodeTiled
+  // query-stationary kernel (gemm_ts.cuh)
+  CUtensorMap map_x_ts;
+  const void* ts_rows = nullptr;
+  int64_t ts_capacity = -1;
+  int ts_nt = 0;
+  int occ_c = 0, occ_clusters = 0;
+  size_t occ_smem = 0;
 };
 inline void gemm_state_free(GemmState* g) {
   if (g->qh) cudaFree(g->qh);
   g->qh = nullptr; g->qh_bytes = 0; g->map_rows = nullptr; g->map_capacity = -1;
+  g->ts_rows = nullptr; g->ts_capacity = -1; g->ts_nt = 0;
 }
 
 }  // namespace ragb

@@ -7,6 +7,7 @@
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <string>
@@ -14,6 +15,7 @@
 
 #include "common.cuh"
 #include "gemm_topk.cuh"
+#include "gemm_ts.cuh"
 #include "ingest.cuh"
 #include "merge.cuh"
 #include "scan.cuh"
@@ -80,6 +82,28 @@ struct ragb_store {
   void* io = nullptr;  // device mirror of pin
   size_t io_bytes = 0;
   GemmState gemm;  // tensor maps etc. of the batched path
+  // optional timing of the dominant search kernel (scan or gemm) with CUDA events on the
+  // launching stream; guarded by search_mu
+  bool profile = false;
+  std::vector<std::pair<cudaEvent_t, cudaEvent_t>> prof_events;
+  size_t prof_used = 0;
+};
+
+// brackets one kernel launch with events when profiling is on
+struct ProfScope {
+  ragb_store* s; cudaStream_t st; cudaEvent_t stop = nullptr;
+  ProfScope(ragb_store* s_, cudaStream_t st_) : s(s_), st(st_) {
+    if (!s->profile) return;
+    if (s->prof_used == s->prof_events.size()) {
+      cudaEvent_t a, b;
+      if (cudaEventCreate(&a) != cudaSuccess || cudaEventCreate(&b) != cudaSuccess) return;
+      s->prof_events.emplace_back(a, b);
+    }
+    auto& ev = s->prof_events[s->prof_used++];
+    cudaEventRecord(ev.first, st);
+    stop = ev.second;
+  }
+  ~ProfScope() { if (stop) cudaEventRecord(stop, st); }
 };
 
 struct DeviceGuard {
@@ -162,6 +186,7 @@ extern "C" int ragb_store_destroy(ragb_store* s) {
     cudaFree(s->rows); cudaFree(s->norms); cudaFree(s->ws); cudaFree(s->stage_dev); cudaFree(s->io);
     if (s->stage_host) cudaFreeHost(s->stage_host);
     if (s->pin) cudaFreeHost(s->pin);
+    for (auto& ev : s->prof_events) { cudaEventDestroy(ev.first); cudaEventDestroy(ev.second); }
     cudaStreamDestroy(s->stream);
   }
   delete s;
@@ -576,9 +601,126 @@ static int rescore_launch(ragb_store* s, const float* q, int64_t nq, int metric,
   return RAGB_OK;
 }
 
+static int env_int(const char* name, int dflt) {
+  const char* v = getenv(name);
+  return (v && *v) ? atoi(v) : dflt;
+}
+
+// merge the per-split lists, optionally re-score the winners in fp32, decode
+static int gemm_finish(ragb_store* s, const float* q, int64_t nq, int k, int kpad, int metric, float threshold,
+                       int flags, uint32_t id_base, const uint64_t* parts, int splits, uint64_t* tmp,
+                       uint64_t* out_keys, float* out_scores, int64_t* out_ids, cudaStream_t st) {
+  const bool rescore = !(flags & RAGB_NO_RESCORE);
+  if (!rescore)
+    return merge_launch(parts, nq, splits, kpad, (int64_t)splits * kpad, kpad, k, out_scores, out_ids, out_keys, st);
+  RB_TRY(merge_launch(parts, nq, splits, kpad, (int64_t)splits * kpad, kpad, k, nullptr, nullptr, tmp, st));
+  if (s->dtype == RAGB_BF16) RB_TRY(rescore_launch<__nv_bfloat16>(s, q, nq, metric, flags, threshold, id_base, kpad, tmp, st));
+  else RB_TRY(rescore_launch<__half>(s, q, nq, metric, flags, threshold, id_base, kpad, tmp, st));
+  return merge_launch(tmp, nq, 1, kpad, kpad, kpad, k, out_scores, out_ids, out_keys, st, /*unsorted=*/true);
+}
+
+// query-stationary tcgen05 kernel (gemm_ts.cuh); returns RAGB_EUNSUPPORTED when the shape does not fit
+static int gemm_ts_search(ragb_store* s, const float* q, int64_t nq, int k, int metric, float threshold, int flags,
+                          int64_t rb, int64_t re, const uint8_t* valid, uint32_t id_base, uint64_t* out_keys,
+                          float* out_scores, int64_t* out_ids, cudaStream_t st) {
+  GemmState* g = &s->gemm;
+  const int kpad = kpad_of(k);
+  const int n_kb = (s->dim + kGemmKB - 1) / kGemmKB;
+  // mode: queries streamed with the corpus (nt = 256, every TMEM column an accumulator) unless
+  // RAGB_TS=1 asks for the TMEM-resident query tile (nt limited by the columns left over)
+  const bool ts = env_int("RAGB_TS", 0) != 0;
+  int nt = 256;
+  if (ts) {
+    nt = n_kb <= 8 ? 128 : n_kb <= 12 ? 64 : n_kb <= 14 ? 32 : 0;
+    if (!nt) return RAGB_EUNSUPPORTED;
+  }
+  nt = env_int("RAGB_TS_NT", nt);
+  if ((ts ? n_kb * 32 : 0) + 2 * nt > 512 || nt % 32 != 0 || nt < 32) return fail(RAGB_EINVAL, "RAGB_TS_NT=%d does not fit TMEM", nt);
+  int kbs = env_int("RAGB_TS_KBS", ts ? (nt == 128 ? 2 : 4) : 1);
+  if (kbs > n_kb) kbs = n_kb;
+  if (kbs < 1) kbs = 1;
+  const size_t stage_bytes = (size_t)kbs * ((size_t)nt * 128 + (ts ? 0 : kStageBytesA));
+  const size_t fixed = 1024 + (size_t)kGemmM * kTsCandStride * 8 + (2 * kTsMaxStages + 5) * 8 + 16;
+  int stages = (int)((232448 - fixed) / stage_bytes);
+  if (stages > kTsMaxStages) stages = kTsMaxStages;
+  stages = std::min(stages, std::max(2, env_int("RAGB_TS_STAGES", stages)));
+  if (stages < 2) return RAGB_EUNSUPPORTED;
+  const size_t smem = fixed + (size_t)stages * stage_bytes;
+
+  if (g->ts_rows != s->rows || g->ts_capacity != s->capacity || g->ts_nt != nt) {
+    RB_TRY(make_map(g, &g->map_x_ts, s->dtype, s->rows, s->dim, s->capacity, s->ld, nt));
+    g->ts_rows = s->rows; g->ts_capacity = s->capacity; g->ts_nt = nt;
+  }
+  const int n_qt = (int)((nq + kGemmM - 1) / kGemmM);
+  const int64_t nq_pad = (int64_t)n_qt * kGemmM;
+  RB_TRY(grow(&g->qh, &g->qh_bytes, (size_t)nq_pad * s->ld * 2, false));
+  if (s->dtype == RAGB_BF16)
+    convert_queries_kernel<__nv_bfloat16><<<(unsigned)(nq_pad / 4), 128, 0, st>>>(q, nq, s->dim, s->ld, metric, (__nv_bfloat16*)g->qh);
+  else
+    convert_queries_kernel<__half><<<(unsigned)(nq_pad / 4), 128, 0, st>>>(q, nq, s->dim, s->ld, metric, (__half*)g->qh);
+  LAUNCHED();
+
+  CUtensorMap map_q;
+  RB_TRY(make_map(g, &map_q, s->dtype, g->qh, s->dim, nq_pad, s->ld, kGemmM));
+  auto kern = ts ? gemm_topk_ts_kernel<true> : gemm_topk_ts_kernel<false>;
+  static bool attr_set[2] = {false, false};
+  if (!attr_set[ts]) {
+    CU_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448));
+    attr_set[ts] = true;
+  }
+  // cluster size: the largest power of two <= 8 dividing the number of query tiles
+  int C = 1;
+  while (C < 8 && n_qt % (2 * C) == 0) C *= 2;
+  C = std::min(C, std::max(1, env_int("RAGB_TS_CLUSTER", C)));
+  cudaLaunchConfig_t cfg = {};
+  cudaLaunchAttribute attr[1];
+  cfg.blockDim = dim3(kGemmThreads); cfg.dynamicSmemBytes = smem; cfg.stream = st;
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = (unsigned)C; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr; cfg.numAttrs = 1;
+  // co-resident clusters decide how many row splits run side by side
+  int max_clusters = s->n_sm / C;
+  if (C > 1) {
+    if (g->occ_c != C || g->occ_smem != smem + (ts ? 1 : 0)) {
+      cfg.gridDim = dim3((unsigned)(C * (s->n_sm / C)));
+      int nc = 0;
+      CU_TRY(cudaOccupancyMaxActiveClusters(&nc, kern, &cfg));
+      g->occ_c = C; g->occ_smem = smem + (ts ? 1 : 0); g->occ_clusters = nc;
+    }
+    if (g->occ_clusters > 0) max_clusters = g->occ_clusters;
+  }
+  const int cps = n_qt / C;
+  TsParams p;
+  p.qh = g->qh; p.ld_q = s->ld; p.n_kb = n_kb; p.nt = nt; p.kbs = kbs; p.stages = stages; p.cluster = C;
+  p.row_begin = rb; p.row_end = re; p.valid = valid; p.nq = nq; p.n_qt = n_qt;
+  p.n_tiles = (re - rb + nt - 1) / nt;
+  int splits = std::max(1, max_clusters / cps);
+  if (splits > p.n_tiles) splits = (int)p.n_tiles;
+  p.n_splits = splits;
+  p.flags = flags; p.threshold = threshold; p.k = k; p.kpad = kpad;
+  p.id_base = id_base; p.idesc = umma_idesc(s->dtype == RAGB_BF16, kGemmM, nt);
+  const size_t part_bytes = (size_t)nq_pad * splits * kpad * sizeof(uint64_t);
+  const size_t tmp_bytes = (size_t)nq * kpad * sizeof(uint64_t);
+  RB_TRY(grow(&s->ws, &s->ws_bytes, part_bytes + tmp_bytes, false));
+  p.out = (uint64_t*)s->ws;
+  uint64_t* tmp = (uint64_t*)((char*)s->ws + part_bytes);
+  cfg.gridDim = dim3((unsigned)(n_qt * splits));
+  {
+    ProfScope prof(s, st);
+    CU_TRY(cudaLaunchKernelEx(&cfg, kern, map_q, g->map_x_ts, p));
+  }
+  LAUNCHED();
+  return gemm_finish(s, q, nq, k, kpad, metric, threshold, flags, id_base, p.out, splits, tmp, out_keys, out_scores,
+                     out_ids, st);
+}
+
 static int gemm_search(ragb_store* s, const float* q, int64_t nq, int k, int metric, float threshold, int flags,
                        int64_t rb, int64_t re, const uint8_t* valid, uint32_t id_base, uint64_t* out_keys,
                        float* out_scores, int64_t* out_ids, cudaStream_t st) {
+  if (!env_int("RAGB_GEMM_SS", 0)) {
+    int r = gemm_ts_search(s, q, nq, k, metric, threshold, flags, rb, re, valid, id_base, out_keys, out_scores, out_ids, st);
+    if (r != RAGB_EUNSUPPORTED) return r;
+  }
   GemmState* g = &s->gemm;
   const int kpad = kpad_of(k);
   if (g->map_rows != s->rows || g->map_capacity != s->capacity) {
@@ -615,15 +757,13 @@ static int gemm_search(ragb_store* s, const float* q, int64_t nq, int k, int met
     CU_TRY(cudaFuncSetAttribute(gemm_topk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448));
     attr_set = true;
   }
-  gemm_topk_kernel<<<(unsigned)(n_qt * splits), kGemmThreads, smem, st>>>(map_q, g->map_x, p);
+  {
+    ProfScope prof(s, st);
+    gemm_topk_kernel<<<(unsigned)(n_qt * splits), kGemmThreads, smem, st>>>(map_q, g->map_x, p);
+  }
   LAUNCHED();
-  const bool rescore = !(flags & RAGB_NO_RESCORE);
-  if (!rescore)
-    return merge_launch(p.out, nq, splits, kpad, (int64_t)splits * kpad, kpad, k, out_scores, out_ids, out_keys, st);
-  RB_TRY(merge_launch(p.out, nq, splits, kpad, (int64_t)splits * kpad, kpad, k, nullptr, nullptr, tmp, st));
-  if (s->dtype == RAGB_BF16) RB_TRY(rescore_launch<__nv_bfloat16>(s, q, nq, metric, flags, threshold, id_base, kpad, tmp, st));
-  else RB_TRY(rescore_launch<__half>(s, q, nq, metric, flags, threshold, id_base, kpad, tmp, st));
-  return merge_launch(tmp, nq, 1, kpad, kpad, kpad, k, out_scores, out_ids, out_keys, st, /*unsorted=*/true);
+  return gemm_finish(s, q, nq, k, kpad, metric, threshold, flags, id_base, p.out, splits, tmp, out_keys, out_scores,
+                     out_ids, st);
 }
 
 static int check_search_args(ragb_store* s, const void* q, int64_t nq, int k, int metric, int64_t* rb, int64_t* re) {
@@ -663,7 +803,10 @@ static int search_core(ragb_store* s, const float* q, int64_t nq, int k, int met
     const int64_t m = std::min(q_step, nq - q0);
     p.q = q + (size_t)q0 * s->dim;
     p.out = (uint64_t*)s->ws;
-    RB_TRY(scan_launch(s->dtype, p, m, s->n_sm, st, &n_lists));
+    {
+      ProfScope prof(s, st);
+      RB_TRY(scan_launch(s->dtype, p, m, s->n_sm, st, &n_lists));
+    }
     RB_TRY(merge_launch((const uint64_t*)s->ws, m, n_lists, kpad, (int64_t)n_lists * kpad, kpad, k,
                         out_scores ? out_scores + q0 * k : nullptr, out_ids ? out_ids + q0 * k : nullptr,
                         out_keys ? out_keys + q0 * kpad : nullptr, st));
@@ -722,6 +865,30 @@ extern "C" int ragb_search(ragb_store* s, const float* q, int64_t nq, int k, int
   CU_TRY(cudaStreamSynchronize(s->stream));
   memcpy(out_scores, h + o_s, sb);
   memcpy(out_ids, h + o_i, ib);
+  return RAGB_OK;
+}
+
+extern "C" int ragb_store_profile(ragb_store* s, int enable) {
+  if (!s) return fail(RAGB_EINVAL, "store is NULL");
+  std::lock_guard<std::mutex> ls(s->search_mu);
+  s->profile = enable != 0;
+  s->prof_used = 0;
+  return RAGB_OK;
+}
+extern "C" int ragb_store_profile_read(ragb_store* s, double* total_ms, int64_t* n_launches) {
+  if (!s) return fail(RAGB_EINVAL, "store is NULL");
+  std::lock_guard<std::mutex> ls(s->search_mu);
+  ON_DEVICE(s->device);
+  double tot = 0;
+  for (size_t i = 0; i < s->prof_used; ++i) {
+    float ms = 0;
+    CU_TRY(cudaEventSynchronize(s->prof_events[i].second));
+    CU_TRY(cudaEventElapsedTime(&ms, s->prof_events[i].first, s->prof_events[i].second));
+    tot += ms;
+  }
+  if (total_ms) *total_ms = tot;
+  if (n_launches) *n_launches = (int64_t)s->prof_used;
+  s->prof_used = 0;
   return RAGB_OK;
 }
 

@@ -233,6 +233,18 @@ class DeviceStore:
         return keys
 
 
+    # -- measurement ------------------------------------------------------------ #
+    def profile(self, enable: bool = True) -> None:
+        """Bracket the dominant kernel of every later search with CUDA events (bench.py's roofline leg)."""
+        check(self._lib.ragb_store_profile(self._h, 1 if enable else 0))
+
+    def profile_read(self) -> Tuple[float, int]:
+        """(summed kernel milliseconds, bracketed launches) since the last read; waits for the events."""
+        ms, n = C.c_double(0.0), C.c_int64(0)
+        check(self._lib.ragb_store_profile_read(self._h, C.byref(ms), C.byref(n)))
+        return ms.value, n.value
+
+
 def kpad_of(k: int) -> int:
     return int(lib().ragb_kpad(int(k)))
 
