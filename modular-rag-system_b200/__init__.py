@@ -7,6 +7,7 @@
 from ._lib import RagbError, build, lib  # noqa: F401
 from .store import DeviceStore, kpad_of, launch_count, merge_keys_dev  # noqa: F401
 from .sharded import ShardedSearcher, shard_bounds  # noqa: F401
+from .rag_store import B200VectorStore, RAGDocument, RAGQuery, RAGResult, install  # noqa: F401
 
 __all__ = ["DeviceStore", "RagbError", "build", "lib", "kpad_of", "launch_count", "merge_keys_dev",
-           "ShardedSearcher", "shard_bounds"]
+           "ShardedSearcher", "shard_bounds", "B200VectorStore", "RAGDocument", "RAGQuery", "RAGResult", "install"]

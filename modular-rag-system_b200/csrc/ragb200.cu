@@ -609,11 +609,11 @@ static int env_int(const char* name, int dflt) {
 // merge the per-split lists, optionally re-score the winners in fp32, decode
 static int gemm_finish(ragb_store* s, const float* q, int64_t nq, int k, int kpad, int metric, float threshold,
                        int flags, uint32_t id_base, const uint64_t* parts, int splits, uint64_t* tmp,
-                       uint64_t* out_keys, float* out_scores, int64_t* out_ids, cudaStream_t st) {
+                       uint64_t* out_keys, float* out_scores, int64_t* out_ids, cudaStream_t st, int k_sel = 0) {
   const bool rescore = !(flags & RAGB_NO_RESCORE);
   if (!rescore)
     return merge_launch(parts, nq, splits, kpad, (int64_t)splits * kpad, kpad, k, out_scores, out_ids, out_keys, st);
-  RB_TRY(merge_launch(parts, nq, splits, kpad, (int64_t)splits * kpad, kpad, k, nullptr, nullptr, tmp, st));
+  RB_TRY(merge_launch(parts, nq, splits, kpad, (int64_t)splits * kpad, kpad, k_sel > k ? k_sel : k, nullptr, nullptr, tmp, st));
   if (s->dtype == RAGB_BF16) RB_TRY(rescore_launch<__nv_bfloat16>(s, q, nq, metric, flags, threshold, id_base, kpad, tmp, st));
   else RB_TRY(rescore_launch<__half>(s, q, nq, metric, flags, threshold, id_base, kpad, tmp, st));
   return merge_launch(tmp, nq, 1, kpad, kpad, kpad, k, out_scores, out_ids, out_keys, st, /*unsorted=*/true);
@@ -668,10 +668,12 @@ static int gemm_ts_search(ragb_store* s, const float* q, int64_t nq, int k, int 
     CU_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448));
     attr_set[ts] = true;
   }
-  // cluster size: the largest power of two <= 8 dividing the number of query tiles
-  int C = 1;
-  while (C < 8 && n_qt % (2 * C) == 0) C *= 2;
-  C = std::min(C, std::max(1, env_int("RAGB_TS_CLUSTER", C)));
+  // cluster size: pairs measured best on B200 (148 SMs all busy, corpus bytes halved on the crossbar,
+  // HBM traffic within 5% of one pass because sibling clusters hit in L2); RAGB_TS_CLUSTER=4/8 widen it
+  int Cmax = 1;
+  while (Cmax < 8 && n_qt % (2 * Cmax) == 0) Cmax *= 2;
+  int C = std::min(Cmax, std::max(1, env_int("RAGB_TS_CLUSTER", 2)));
+  while (C & (C - 1)) C &= C - 1;  // power of two
   cudaLaunchConfig_t cfg = {};
   cudaLaunchAttribute attr[1];
   cfg.blockDim = dim3(kGemmThreads); cfg.dynamicSmemBytes = smem; cfg.stream = st;
@@ -697,7 +699,10 @@ static int gemm_ts_search(ragb_store* s, const float* q, int64_t nq, int k, int 
   int splits = std::max(1, max_clusters / cps);
   if (splits > p.n_tiles) splits = (int)p.n_tiles;
   p.n_splits = splits;
-  p.flags = flags; p.threshold = threshold; p.k = k; p.kpad = kpad;
+  // with the re-score on, the tensor-core pass (16-bit queries) only SELECTS: keep all kpad >= k slots so that
+  // a candidate the rounding pushed just below the k-th place is still re-scored in fp32
+  const int k_sel = (flags & RAGB_NO_RESCORE) ? k : kpad;
+  p.flags = flags; p.threshold = threshold; p.k = k_sel; p.kpad = kpad;
   p.id_base = id_base; p.idesc = umma_idesc(s->dtype == RAGB_BF16, kGemmM, nt);
   const size_t part_bytes = (size_t)nq_pad * splits * kpad * sizeof(uint64_t);
   const size_t tmp_bytes = (size_t)nq * kpad * sizeof(uint64_t);
@@ -711,7 +716,7 @@ static int gemm_ts_search(ragb_store* s, const float* q, int64_t nq, int k, int 
   }
   LAUNCHED();
   return gemm_finish(s, q, nq, k, kpad, metric, threshold, flags, id_base, p.out, splits, tmp, out_keys, out_scores,
-                     out_ids, st);
+                     out_ids, st, k_sel);
 }
 
 static int gemm_search(ragb_store* s, const float* q, int64_t nq, int k, int metric, float threshold, int flags,

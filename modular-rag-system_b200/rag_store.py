@@ -1,0 +1,396 @@
+"""B200VectorStore — drop-in for the reference's ``RAGVectorStore`` (ollama_rag_system.py:225-554).
+
+Same constructor, methods, attributes, result types and error convention as the reference class;
+what changes is where the vectors live and who scans them:
+
+* content + metadata stay in the reference's own SQLite table (same schema, :275-286);
+* every embedding is also normalised + packed onto the GPU by the ingest kernel — the slot the
+  reference fills with ``faiss.IndexFlatIP`` and never searches (:298-305, :372-386);
+* ``search`` runs the exact scan / threshold / sort / slice of ``_search_sqlite`` (:480-515) on the
+  device (C ABI ``ragb_search``), then reads the winners' content rows back from SQLite by id.
+
+Reference *policy* is kept in this shim with the reference's defaults: cosine
+clamped to [0,1] (:218), ``similarity_threshold`` with ``>=`` (:495), the newest-1000-rows window
+(:474), ``source_filters`` (:466-469), newest-first order among equal scores (:474, :512),
+``access_count + 1`` on returned documents (:504), ``total_documents_searched`` = rows the SQL query
+would have returned (:520).  ``window=None`` lifts the 1000-row cap.
+
+Nothing here raises through ``add_document`` / ``search``: failures print and return ``False`` / an
+empty ``RAGResult`` exactly as the reference does (:319-321, :523-525).  There is no CPU scoring
+path: without the CUDA library the constructor fails loudly.
+"""
+from __future__ import annotations
+
+import hashlib
+import json
+import pickle
+import sqlite3
+import threading
+import time
+from dataclasses import asdict, dataclass
+from pathlib import Path
+from typing import Any, Dict, Iterable, List, Optional, Sequence
+
+import numpy as np
+
+from .store import DeviceStore
+
+NEG_INF = float("-inf")
+
+
+# --------------------------------------------------------------------------- #
+# boundary types: field-for-field mirrors of ollama_rag_system.py:46-93 (duck-compatible with the
+# reference's own dataclasses, which are accepted wherever these are)
+# --------------------------------------------------------------------------- #
+@dataclass
+class RAGDocument:
+    id: str
+    content: str
+    metadata: Dict[str, Any]
+    embedding: Optional[List[float]] = None
+    timestamp: float = 0.0
+    source: str = "unknown"
+    importance_score: float = 1.0
+    access_count: int = 0
+
+    def __post_init__(self):
+        if self.timestamp == 0.0:
+            self.timestamp = time.time()
+        if not self.id:
+            self.id = self.generate_id()
+
+    def generate_id(self) -> str:  # :61-68
+        content_hash = hashlib.md5(self.content.encode()).hexdigest()[:8]
+        time_hash = hashlib.md5(str(self.timestamp).encode()).hexdigest()[:4]
+        return f"{self.source}_{content_hash}_{time_hash}"
+
+    def to_dict(self) -> Dict:
+        return asdict(self)
+
+
+@dataclass
+class RAGQuery:
+    query_text: str
+    context: Dict[str, Any]
+    max_results: int = 5
+    similarity_threshold: float = 0.7
+    source_filters: Optional[List[str]] = None
+    metadata_filters: Optional[Dict[str, Any]] = None
+
+
+@dataclass
+class RAGResult:
+    documents: List[RAGDocument]
+    similarities: List[float]
+    query_embedding: Optional[List[float]] = None
+    retrieval_time: float = 0.0
+    total_documents_searched: int = 0
+
+
+class CacheOnlyEmbedder:
+    """Stand-in for the reference's ``EmbeddingGenerator`` (:96-197) when that module is not importable.
+    The encoder forward / Ollama HTTP call is out of scope: this object only serves vectors that were
+    put into ``embedding_cache`` (the reference checks the same cache first, :116-117)."""
+
+    def __init__(self):
+        self.embedding_cache: Dict[str, List[float]] = {}
+
+    def generate_embedding(self, text: str) -> List[float]:
+        if text in self.embedding_cache:
+            return self.embedding_cache[text]
+        raise RuntimeError("no encoder configured: put the vector into embedding_generator.embedding_cache "
+                           "or pass an embedding_generator with generate_embedding(text)")
+
+
+def _default_embedder():
+    try:  # the reference's own generator when its module is importable (unchanged, out of scope)
+        from ollama_rag_system import EmbeddingGenerator  # type: ignore
+        return EmbeddingGenerator()
+    except Exception:
+        return CacheOnlyEmbedder()
+
+
+class B200VectorStore:
+    """Vector storage and retrieval for RAG with the embedding store on a B200 (see module docstring)."""
+
+    def __init__(self, storage_path: Path, use_chromadb: bool = True, *, dtype: str = "fp16", device: int = 0,
+                 window: Optional[int] = 1000, capacity: int = 4096, embedding_generator=None,
+                 result_types=None):
+        self.storage_path = Path(storage_path)
+        self.storage_path.mkdir(parents=True, exist_ok=True)
+        self.use_chromadb = False            # the exact path is the SQLite + device path
+        self.embedding_generator = embedding_generator or _default_embedder()
+        self.faiss_index = None              # the device store takes this slot (:242, :298-305)
+        self.document_mapping: Dict[int, str] = {}   # device row -> doc id (:243, :383)
+        self.window = window
+        self.dtype, self.device = dtype, int(device)
+        self._capacity0 = int(capacity)
+        self._types = result_types or (RAGDocument, RAGResult)
+        self._lock = threading.RLock()
+        self._store: Optional[DeviceStore] = None     # created when the first vector fixes the dimension (D4)
+        self._n = 0
+        self._ts = np.zeros(0, np.float64)            # per device row
+        self._src = np.zeros(0, np.int32)
+        self._live = np.zeros(0, bool)                # False once the id was replaced (:351)
+        self._has = np.zeros(0, bool)                 # False for NULL embeddings (:485-492)
+        self._row_of: Dict[str, int] = {}
+        self._src_code: Dict[str, int] = {}
+        self._monotone = True                         # timestamps non-decreasing in row order
+        self._init_sqlite_fallback()
+        self._rebuild_from_sqlite()
+        print(f"✅ RAG Vector Store initialized: {storage_path}")
+
+    # -- storage (same table as the reference, :270-296) ------------------------------------ #
+    def _init_sqlite_fallback(self):
+        self.db_path = self.storage_path / "rag_documents.db"
+        with sqlite3.connect(self.db_path) as conn:
+            conn.execute("""
+                CREATE TABLE IF NOT EXISTS documents (
+                    id TEXT PRIMARY KEY, content TEXT NOT NULL, metadata TEXT, embedding BLOB,
+                    timestamp REAL, source TEXT, importance_score REAL, access_count INTEGER)""")
+            conn.execute("CREATE INDEX IF NOT EXISTS idx_timestamp ON documents(timestamp);")
+            conn.execute("CREATE INDEX IF NOT EXISTS idx_source ON documents(source);")
+
+    def _rebuild_from_sqlite(self):
+        """The device store is a cache of the table: refill it on open (the reference's FAISS index is
+        volatile and never rebuilt, :298-305)."""
+        with sqlite3.connect(self.db_path) as conn:
+            rows = conn.execute("SELECT id, embedding, timestamp, source FROM documents ORDER BY rowid").fetchall()
+        batch: List[tuple] = []
+        for doc_id, blob, ts, source in rows:
+            emb = None
+            if blob:
+                try:
+                    emb = pickle.loads(blob)
+                except Exception:
+                    emb = None
+            batch.append((doc_id, emb, ts, source))
+        if batch:
+            self._append_rows(batch)
+
+    # -- host-side row table ------------------------------------------------------------------ #
+    def _grow_meta(self, need: int):
+        if need <= len(self._ts):
+            return
+        cap = max(need, 2 * len(self._ts), 1024)
+        for name in ("_ts", "_src", "_live", "_has"):
+            old = getattr(self, name)
+            new = np.zeros(cap, old.dtype)
+            new[: len(old)] = old
+            setattr(self, name, new)
+
+    def _append_rows(self, items: Sequence[tuple]) -> None:
+        """items: (doc_id, embedding-or-None, timestamp, source).  One device row per item; NULL and
+        wrong-length embeddings become zero rows (they score 0.0, :201-202 / :214-215)."""
+        with self._lock:
+            dim = None if self._store is None else self._store.dim
+            if dim is None:
+                for _, emb, _, _ in items:
+                    if emb is not None and len(emb) > 0:
+                        dim = len(emb)
+                        break
+                if dim is None:
+                    dim = 1  # only NULL embeddings so far; re-created when the first real vector arrives
+                self._store = DeviceStore(dim, self.dtype, max(self._capacity0, len(items)), self.device)
+                self._dim_is_placeholder = all(e is None or len(e) == 0 for _, e, _, _ in items)
+            elif getattr(self, "_dim_is_placeholder", False):
+                real = next((len(e) for _, e, _, _ in items if e is not None and len(e) > 0), None)
+                if real is not None:  # every earlier row is a NULL row: rebuild them as zero rows
+                    n_old = self._n
+                    self._store.close()
+                    self._store = DeviceStore(real, self.dtype, max(self._capacity0, n_old + len(items)), self.device)
+                    if n_old:
+                        self._store.add(np.zeros((n_old, real), np.float32))
+                    self._dim_is_placeholder = False
+                    dim = real
+            X = np.zeros((len(items), dim), np.float32)
+            has = np.zeros(len(items), bool)
+            for i, (_, emb, _, _) in enumerate(items):
+                if emb is not None and len(emb) == dim:
+                    X[i] = np.asarray(emb, dtype=np.float32)
+                    has[i] = True
+                elif emb is not None and len(emb) > 0:
+                    has[i] = True  # wrong length: a real row that scores 0.0 against every query
+            first = self._store.add(X)
+            assert first == self._n
+            self._grow_meta(self._n + len(items))
+            for i, (doc_id, _, ts, source) in enumerate(items):
+                r = first + i
+                old = self._row_of.get(doc_id)
+                if old is not None:
+                    self._live[old] = False  # INSERT OR REPLACE (:351)
+                self._row_of[doc_id] = r
+                self.document_mapping[r] = doc_id
+                t = float(ts) if ts is not None else 0.0
+                if r > 0 and t < self._ts[r - 1]:
+                    self._monotone = False
+                self._ts[r] = t
+                self._src[r] = self._src_code.setdefault(source, len(self._src_code))
+                self._live[r] = True
+                self._has[r] = has[i]
+            self._n += len(items)
+
+    # -- ingest (:307-321, :346-370, :372-386) ------------------------------------------------ #
+    def add_document(self, document) -> bool:
+        """Add one document; returns False (and prints) on any failure, like the reference."""
+        try:
+            return self.add_documents([document])[0]
+        except Exception as e:
+            print(f"Error adding document: {e}")
+            return False
+
+    def add_documents(self, documents: Iterable) -> List[bool]:
+        """Batched ingest: one SQLite transaction (``executemany``) and one normalise+pack launch for the
+        whole batch instead of a commit and a FAISS append per document (:349-363, :379-383)."""
+        docs = list(documents)
+        ok = [False] * len(docs)
+        rows, items, idx = [], [], []
+        for i, d in enumerate(docs):
+            try:
+                if not d.embedding:  # :311-312
+                    d.embedding = self.embedding_generator.generate_embedding(d.content)
+                emb = list(d.embedding) if d.embedding is not None and len(d.embedding) else None
+                rows.append((d.id, d.content, json.dumps(d.metadata), pickle.dumps(emb) if emb else None,
+                             d.timestamp, d.source, d.importance_score, d.access_count))
+                items.append((d.id, emb, d.timestamp, d.source))
+                idx.append(i)
+            except Exception as e:
+                print(f"Error adding document: {e}")
+        if not rows:
+            return ok
+        try:
+            with self._lock:
+                with sqlite3.connect(self.db_path) as conn:
+                    conn.executemany("""INSERT OR REPLACE INTO documents
+                        (id, content, metadata, embedding, timestamp, source, importance_score, access_count)
+                        VALUES (?, ?, ?, ?, ?, ?, ?, ?)""", rows)
+                self._append_rows(items)
+            for i in idx:
+                ok[i] = True
+        except Exception as e:
+            print(f"SQLite add error: {e}")
+        return ok
+
+    # -- retrieve (:388-403, :454-525) -------------------------------------------------------- #
+    def _candidate_rows(self, source_filters):
+        """(valid mask over device rows, rows the SQL query of :462-477 would return)."""
+        n = self._n
+        m = self._live[:n].copy()
+        if source_filters:
+            codes = [self._src_code[s] for s in source_filters if s in self._src_code]
+            m &= np.isin(self._src[:n], codes)
+        total = int(m.sum())
+        if self.window is not None and total > self.window:
+            rows = np.flatnonzero(m)
+            if self._monotone:
+                keep = rows[-self.window:]
+            else:  # newest `window` by timestamp; later row wins a timestamp tie
+                order = np.lexsort((rows, self._ts[rows]))
+                keep = rows[order[-self.window:]]
+            m = np.zeros(n, bool)
+            m[keep] = True
+            total = self.window
+        return m & self._has[:n], total
+
+    def search(self, query) -> Any:
+        """Exact top-``max_results`` of the stored documents for ``query`` (a ``RAGQuery``)."""
+        Doc, Res = self._types
+        start_time = time.time()
+        try:
+            query_embedding = self.embedding_generator.generate_embedding(query.query_text)
+            results = self._search_device(query, query_embedding)
+        except Exception as e:
+            print(f"Device search error: {e}")
+            return Res(documents=[], similarities=[])
+        results.query_embedding = query_embedding
+        results.retrieval_time = time.time() - start_time
+        return results
+
+    def _search_device(self, query, query_embedding):
+        Doc, Res = self._types
+        with self._lock:
+            n, store = self._n, self._store
+            if store is None or n == 0:
+                return Res(documents=[], similarities=[], total_documents_searched=0)
+            valid, total = self._candidate_rows(query.source_filters)
+            monotone = self._monotone
+            ts = self._ts[:n].copy() if not monotone else None
+        k = int(query.max_results)
+        if not query_embedding or k <= 0 or not valid.any():  # :493 — nothing is scored without a query vector
+            return Res(documents=[], similarities=[], total_documents_searched=total)
+        q = np.asarray(query_embedding, dtype=np.float32)
+        thr = float(query.similarity_threshold)
+        n_valid = int(valid.sum())
+        kk = min(k, 1024)
+        while True:
+            ids, sc = store.search(q, kk, "cosine", threshold=thr, clamp01=True, row_end=n, valid=valid.astype(np.uint8))
+            ids, sc = ids[0], sc[0]
+            got = ids >= 0
+            ids, sc = ids[got], sc[got]
+            if monotone or len(ids) < kk or kk >= min(n_valid, 1024) or sc[kk - 1] < sc[min(k, kk) - 1]:
+                break  # the tie group at the cut is complete (or timestamps follow row order)
+            kk = min(1024, 2 * kk)
+        if not monotone and len(ids):  # reference order: score desc, then newer timestamp (:474, :512)
+            order = np.lexsort((-ids, -ts[ids], -sc.astype(np.float64)))
+            ids, sc = ids[order], sc[order]
+        ids, sc = ids[:k], sc[:k]
+        docs = self._fetch_documents([self.document_mapping[int(r)] for r in ids], Doc)
+        return Res(documents=docs, similarities=[float(s) for s in sc], total_documents_searched=total)
+
+    def _fetch_documents(self, doc_ids: List[str], Doc) -> List[Any]:
+        if not doc_ids:
+            return []
+        out: Dict[str, Any] = {}
+        with sqlite3.connect(self.db_path) as conn:
+            for i in range(0, len(doc_ids), 500):
+                chunk = doc_ids[i:i + 500]
+                cur = conn.execute("SELECT * FROM documents WHERE id IN (%s)" % ",".join("?" * len(chunk)), chunk)
+                for doc_id, content, meta, blob, ts, source, imp, acc in cur.fetchall():
+                    out[doc_id] = Doc(id=doc_id, content=content, metadata=json.loads(meta) if meta else {},
+                                      embedding=pickle.loads(blob) if blob else None, timestamp=ts, source=source,
+                                      importance_score=imp, access_count=(acc or 0) + 1)  # :495-505
+        return [out[d] for d in doc_ids if d in out]
+
+    # -- stats / life cycle (:527-554) ------------------------------------------------------------ #
+    def get_stats(self) -> Dict[str, Any]:
+        stats = {'backend': 'b200+sqlite', 'total_documents': 0, 'sources': {},
+                 'embedding_cache_size': len(getattr(self.embedding_generator, 'embedding_cache', {})),
+                 'device_rows': self._n, 'dtype': self.dtype, 'gpus': 1, 'device': self.device,
+                 'dim': None if self._store is None else self._store.dim}
+        try:
+            with sqlite3.connect(self.db_path) as conn:
+                stats['total_documents'] = conn.execute("SELECT COUNT(*) FROM documents").fetchone()[0]
+                stats['sources'] = dict(conn.execute("SELECT source, COUNT(*) FROM documents GROUP BY source").fetchall())
+        except Exception as e:
+            print(f"Stats error: {e}")
+        return stats
+
+    def close(self) -> None:
+        with self._lock:
+            if self._store is not None:
+                self._store.close()
+                self._store = None
+
+
+def install(**store_kwargs) -> None:
+    """Swap the device store into the reference in place (what INTEGRATION.md describes): after
+    ``install()`` ``ollama_rag_system.RAGSystem`` builds a ``B200VectorStore`` and gains the
+    ``add_documents`` entry point four callers already assume (SURVEY.md §3.5 D2:
+    enhanced_rag_system.py:337,1194; embedding_pipeline.py:806; run_integrated_rag.py:284)."""
+    import ollama_rag_system as ref  # the unmodified reference module must be importable
+
+    class _Installed(B200VectorStore):
+        def __init__(self, storage_path, use_chromadb: bool = True):
+            super().__init__(storage_path, use_chromadb, result_types=(ref.RAGDocument, ref.RAGResult), **store_kwargs)
+
+    def add_documents(self, documents) -> List[str]:
+        """Batched ingest entry point; returns the ids of the documents that were stored."""
+        docs = list(documents)
+        for d in docs:
+            if not getattr(d, "id", None):
+                d.id = d.generate_id()
+        ok = self.vector_store.add_documents(docs)
+        return [d.id for d, good in zip(docs, ok) if good]
+
+    ref.RAGVectorStore = _Installed
+    ref.RAGSystem.add_documents = add_documents

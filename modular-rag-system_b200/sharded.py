@@ -84,7 +84,7 @@ class ShardedSearcher:
         import torch
         if self._keys is None or self._keys.shape != (nq, kpad):
             self._keys = torch.empty((nq, kpad), dtype=torch.int64, device=device)
-            self._gathered = torch.empty((self.world, nq, kpad), dtype=torch.int64, device=device)
+            self._gathered = torch.empty((self.world * nq, kpad), dtype=torch.int64, device=device)
         return self._keys, self._gathered
 
     def search_dev(self, q, k: int, metric: str = "ip", threshold: float = NEG_INF, clamp01: bool = False,
@@ -97,7 +97,7 @@ class ShardedSearcher:
         if self.world == 1:
             return merge_keys_dev(keys.unsqueeze(0), k, self.store.device)
         self.dist.all_gather_into_tensor(gathered, keys, group=self.group)
-        return merge_keys_dev(gathered, k, self.store.device)
+        return merge_keys_dev(gathered.view(self.world, q.shape[0], kpad), k, self.store.device)
 
     def search(self, q: np.ndarray, k: int, metric: str = "ip", threshold: float = NEG_INF, clamp01: bool = False,
                flags: int = 0) -> Tuple[np.ndarray, np.ndarray]:

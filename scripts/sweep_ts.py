@@ -23,6 +23,10 @@ def run(n, d, nq, envs, iters=5):
 
 if __name__ == "__main__":
     which = sys.argv[1] if len(sys.argv) > 1 else "a"
+    if which == "e":
+        run(4_000_000, 768, 1024, [dict(RAGB_TS_NT=nt, RAGB_TS_KBS=kbs, RAGB_TS_CLUSTER=1) for nt, kbs in ((128, 1), (128, 2), (128, 3), (64, 1), (64, 2), (64, 4), (64, 6))])
+    if which == "d":
+        run(4_000_000, 768, 1024, [dict(RAGB_TS_NT=nt, RAGB_TS_CLUSTER=c) for nt in (256, 192, 128) for c in (2, 1)])
     if which == "c":
         for n, d in ((4_000_000, 768), (2_000_000, 384)):
             run(n, d, 1024, [dict(RAGB_TS_CLUSTER=c) for c in (8, 4, 2, 1)] + [dict(RAGB_TS_NT=128, RAGB_TS_CLUSTER=8), dict(RAGB_TS=1), dict(RAGB_GEMM_SS=1)])

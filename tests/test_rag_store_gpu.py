@@ -1,0 +1,138 @@
+"""B200VectorStore (drop-in for RAGVectorStore) against the unmodified reference's outputs (golden
+fixtures made by oracle/make_golden.py): same documents, same query, same policy -> same documents back."""
+import numpy as np
+import pytest
+
+from oracle import ref_search
+from helpers import SEARCH_FIXTURES, load
+
+pytestmark = pytest.mark.gpu
+
+
+def _build(fx, tmp_path, **kw):
+    from modular_rag_system_b200 import B200VectorStore, RAGDocument
+    vs = B200VectorStore(tmp_path / "store", **kw)
+    null = set(fx["null_rows"].tolist())
+    docs = []
+    for i in range(len(fx["X"])):
+        docs.append(RAGDocument(id=str(fx["doc_ids"][i]), content=f"doc {i}", metadata={"row": i},
+                                embedding=None if i in null else fx["X"][i].astype(np.float64).tolist(),
+                                timestamp=float(fx["ts"][i]), source=str(fx["sources"][i])))
+    return vs, docs
+
+
+class _NullEmbedder:
+    """generate_embedding returns nothing for documents (NULL embedding rows, :485-492); queries come from the cache."""
+    def __init__(self):
+        self.embedding_cache = {}
+
+    def generate_embedding(self, text):
+        return self.embedding_cache.get(text)
+
+
+@pytest.mark.parametrize("name", SEARCH_FIXTURES)
+def test_matches_reference_outputs(name, tmp_path):
+    from modular_rag_system_b200 import RAGQuery
+    fx = load(name)
+    vs, docs = _build(fx, tmp_path, embedding_generator=_NullEmbedder())
+    assert all(vs.add_documents(docs)) or len(docs) == 0
+    vs.embedding_generator.embedding_cache["Q"] = fx["q"].astype(np.float64).tolist()
+    k, thr = int(fx["k"]), float(fx["thr"])
+    res = vs.search(RAGQuery(query_text="Q", context={}, max_results=k, similarity_threshold=thr,
+                             source_filters=fx["source_filters"].tolist() or None))
+    assert res.total_documents_searched == int(fx["ref_total"])
+    assert len(res.documents) == len(res.similarities) <= k
+    # map returned ids back to fixture rows (the LAST row carrying an id is the live one)
+    last = {str(d): i for i, d in enumerate(fx["doc_ids"].tolist())}
+    got_rows = np.array([last[d.id] for d in res.documents], dtype=np.int64)
+    ref_rows, ref_sims = fx["ref_rows"], fx["ref_sims"]
+    X64 = fx["X"].astype(np.float64)
+    q64 = fx["q"].astype(np.float64)
+
+    def score_of(rows):
+        den = np.linalg.norm(X64[rows], axis=1) * np.linalg.norm(q64)
+        s = np.divide(X64[rows] @ q64, den, out=np.zeros(len(rows)), where=den != 0)
+        return np.clip(s, 0.0, 1.0)
+
+    pad = lambda a, v: np.pad(a, (0, k - len(a)), constant_values=v)
+    err = ref_search.check_topk(pad(got_rows, -1), pad(np.array(res.similarities), -np.inf), pad(ref_rows, -1),
+                                pad(ref_sims, -np.inf), score_of, 1e-3, thr)
+    assert err is None, err
+    if "edge" in name or "planted" in name:  # separated scores or exact ties: identical order, newest first
+        assert got_rows.tolist() == ref_rows.tolist()
+    for d, r in zip(res.documents, got_rows):
+        assert d.content == f"doc {r}" and d.metadata == {"row": int(r)} and d.access_count == 1
+    assert res.query_embedding is not None and res.retrieval_time > 0
+    vs.close()
+
+
+def test_error_conventions_and_stats(tmp_path):
+    from modular_rag_system_b200 import B200VectorStore, RAGDocument, RAGQuery
+    vs = B200VectorStore(tmp_path / "s")
+    r = vs.search(RAGQuery("nothing cached", {}))            # embedder fails -> empty result, no raise (:523-525)
+    assert r.documents == [] and r.similarities == []
+    assert vs.add_document(RAGDocument(id="a", content="x", metadata={})) is False  # cannot embed -> False (:319-321)
+    rng = np.random.default_rng(0)
+    X = rng.standard_normal((50, 96))
+    assert all(vs.add_documents([RAGDocument(id=f"d{i}", content=str(i), metadata={}, embedding=X[i].tolist(),
+                                             source="a" if i % 2 else "b") for i in range(50)]))
+    assert vs.add_document(RAGDocument(id="short", content="s", metadata={}, embedding=[1.0, 2.0]))  # wrong length
+    vs.embedding_generator.embedding_cache["q"] = X[7].tolist()
+    r = vs.search(RAGQuery("q", {}, max_results=3, similarity_threshold=0.7))
+    assert [d.id for d in r.documents] == ["d7"] and abs(r.similarities[0] - 1.0) < 1e-3
+    r = vs.search(RAGQuery("q", {}, max_results=60, similarity_threshold=0.0))
+    assert len(r.documents) == 51 and r.documents[0].id == "d7"   # the wrong-length row scores 0.0 and still returns
+    vs.embedding_generator.embedding_cache["bad"] = [1.0, 2.0, 3.0]  # wrong-length query scores 0.0 everywhere
+    r = vs.search(RAGQuery("bad", {}, max_results=4, similarity_threshold=0.0))
+    assert [d.id for d in r.documents] == ["short", "d49", "d48", "d47"] and r.similarities == [0.0] * 4
+    st = vs.get_stats()
+    assert st["backend"] == "b200+sqlite" and st["total_documents"] == 51 and st["sources"]["a"] == 25
+    assert vs.document_mapping[7] == "d7" and vs.faiss_index is None and vs.db_path.exists()
+    vs.close()
+
+
+def test_reopen_rebuilds_device_store(tmp_path):
+    from modular_rag_system_b200 import B200VectorStore, RAGDocument, RAGQuery
+    rng = np.random.default_rng(1)
+    X = rng.standard_normal((300, 64))
+    vs = B200VectorStore(tmp_path / "s", window=None)
+    vs.add_documents([RAGDocument(id=f"d{i}", content=str(i), metadata={}, embedding=X[i].tolist(), timestamp=1000.0 + i)
+                      for i in range(300)])
+    vs.close()
+    vs2 = B200VectorStore(tmp_path / "s", window=None)
+    vs2.embedding_generator.embedding_cache["q"] = X[123].tolist()
+    r = vs2.search(RAGQuery("q", {}, max_results=2, similarity_threshold=0.5))
+    assert r.documents[0].id == "d123" and r.total_documents_searched == 300
+    vs2.close()
+
+
+def test_concurrent_writer_and_readers(tmp_path):
+    """One ingest thread (the reference's worker, :652) against reader threads (rag_query_interface.py:740)."""
+    import threading
+    from modular_rag_system_b200 import B200VectorStore, RAGDocument, RAGQuery
+    rng = np.random.default_rng(2)
+    X = rng.standard_normal((400, 128))
+    vs = B200VectorStore(tmp_path / "s", window=None, capacity=64)
+    vs.add_documents([RAGDocument(id="d0", content="0", metadata={}, embedding=X[0].tolist())])
+    vs.embedding_generator.embedding_cache["q"] = X[0].tolist()
+    errors = []
+
+    def writer():
+        for i in range(1, 400, 20):
+            ok = vs.add_documents([RAGDocument(id=f"d{j}", content=str(j), metadata={}, embedding=X[j].tolist())
+                                   for j in range(i, min(400, i + 20))])
+            if not all(ok):
+                errors.append("add failed")
+
+    def reader():
+        for _ in range(30):
+            r = vs.search(RAGQuery("q", {}, max_results=1, similarity_threshold=0.9))
+            if [d.id for d in r.documents] != ["d0"]:
+                errors.append(f"reader saw {[d.id for d in r.documents]}")
+
+    th = [threading.Thread(target=writer)] + [threading.Thread(target=reader) for _ in range(3)]
+    [t.start() for t in th]
+    [t.join() for t in th]
+    assert not errors, errors[:3]
+    assert vs.get_stats()["device_rows"] == 400
+    vs.close()
