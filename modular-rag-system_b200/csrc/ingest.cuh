@@ -112,7 +112,6 @@ __device__ __forceinline__ float block_sum(float v, float* red) {
 }
 
 constexpr int kPoolThreads = 256;
-constexpr int kPoolUnroll = 8;
 
 // dynamic shared memory: float w[seq] | float acc[groups][W][8] | float v[chunks*8] | float red[8]
 template <typename Tin, typename Tm, typename Tout>
@@ -120,6 +119,8 @@ __global__ void __launch_bounds__(kPoolThreads) pool_norm_pack_kernel(
     const Tin* __restrict__ tok, const Tm* __restrict__ mask, int seq, int hidden,
     Tout* __restrict__ out, int64_t ld_out, float* __restrict__ norms, bool vec_ok) {
   extern __shared__ __align__(16) float sm[];
+  // token rows in flight per thread: 16-bit inputs move 16 B per row, so they need twice as many
+  constexpr int kPoolUnroll = sizeof(Tin) == 2 ? 16 : 8;
   const int chunks = (hidden + 7) / 8;
   const int W = chunks < kPoolThreads ? chunks : kPoolThreads;
   const int groups = kPoolThreads / W;
@@ -148,23 +149,44 @@ __global__ void __launch_bounds__(kPoolThreads) pool_norm_pack_kernel(
 #pragma unroll
     for (int e = 0; e < 8; ++e) acc[e] = 0.f;
     if (active && c < chunks) {
+      constexpr int NV = sizeof(Tin) == 2 ? 1 : 2;  // 16-byte loads per 8 elements
+      const bool fast = vec_ok && (c * 8 + 8 <= hidden);
       for (int s0 = g; s0 < seq; s0 += groups * kPoolUnroll) {
-        float f[kPoolUnroll][8];
         float ws[kPoolUnroll];
+        if (fast) {
+          // phase 1: every load of the batch is in flight before anything waits on one
+          uint4 raw[kPoolUnroll][NV];
 #pragma unroll
-        for (int u = 0; u < kPoolUnroll; ++u) {
-          const int s = s0 + u * groups;
-          ws[u] = s < seq ? w[s] : 0.f;
-          if (ws[u] != 0.f) load8_stream(base + (size_t)s * hidden, c, hidden, vec_ok, f[u]);
-          else {
+          for (int u = 0; u < kPoolUnroll; ++u) {
+            const int s = s0 + u * groups;
+            ws[u] = s < seq ? w[s] : 0.f;
+            const Tin* src = base + (size_t)s * hidden + c * 8;
 #pragma unroll
-            for (int e = 0; e < 8; ++e) f[u][e] = 0.f;
+            for (int v = 0; v < NV; ++v)
+              raw[u][v] = ws[u] != 0.f ? ld_stream16(reinterpret_cast<const char*>(src) + 16 * v) : make_uint4(0, 0, 0, 0);
+          }
+          // phase 2: convert and accumulate
+#pragma unroll
+          for (int u = 0; u < kPoolUnroll; ++u) {
+            float f[8];
+            if constexpr (NV == 1) Elem<Tin>::unpack(raw[u][0], f);
+            else { Elem<float>::unpack(raw[u][0], f); Elem<float>::unpack(raw[u][NV - 1], f + 4); }
+#pragma unroll
+            for (int e = 0; e < 8; ++e) acc[e] = fmaf(ws[u], f[e], acc[e]);
+          }
+        } else {
+#pragma unroll
+          for (int u = 0; u < kPoolUnroll; ++u) {
+            const int s = s0 + u * groups;
+            ws[u] = s < seq ? w[s] : 0.f;
+            if (ws[u] != 0.f) {
+              float f[8];
+              load8_stream(base + (size_t)s * hidden, c, hidden, false, f);
+#pragma unroll
+              for (int e = 0; e < 8; ++e) acc[e] = fmaf(ws[u], f[e], acc[e]);
+            }
           }
         }
-#pragma unroll
-        for (int u = 0; u < kPoolUnroll; ++u)
-#pragma unroll
-          for (int e = 0; e < 8; ++e) acc[e] = fmaf(ws[u], f[u][e], acc[e]);
       }
     }
     __syncthreads();
