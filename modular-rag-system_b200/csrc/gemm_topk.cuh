@@ -356,6 +356,11 @@ struct GemmState {
   const void* ts_rows = nullptr;
   int64_t ts_capacity = -1;
   int ts_nt = 0;
+  // SM-pair kernel (gemm_pair.cuh)
+  CUtensorMap map_x_pair;
+  const void* pair_rows = nullptr;
+  int64_t pair_capacity = -1;
+  int pair_clusters = 0;
   int occ_c = 0, occ_clusters = 0;
   size_t occ_smem = 0;
 };
@@ -363,6 +368,7 @@ inline void gemm_state_free(GemmState* g) {
   if (g->qh) cudaFree(g->qh);
   g->qh = nullptr; g->qh_bytes = 0; g->map_rows = nullptr; g->map_capacity = -1;
   g->ts_rows = nullptr; g->ts_capacity = -1; g->ts_nt = 0;
+  g->pair_rows = nullptr; g->pair_capacity = -1;
 }
 
 }  // namespace ragb

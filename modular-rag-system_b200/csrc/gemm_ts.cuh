@@ -255,7 +255,8 @@ gemm_topk_ts_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_cons
     uint64_t* my = cand + (size_t)tid * kTsCandStride;
     uint64_t* warp_cand = cand + (size_t)(quarter * 32) * kTsCandStride;
     int cnt = 0;
-    const float user_fast = fast_bound(p.threshold, p.flags);
+    // rows of the query tile past nq are zero padding: they must never take the candidate path
+    const float user_fast = ((int64_t)qt * kGemmM + tid < p.nq) ? fast_bound(p.threshold, p.flags) : INFINITY;
     float fthr = user_fast;
     uint32_t tt = 0;
     for (int64_t t = t0; t < t1; ++t, ++tt) {

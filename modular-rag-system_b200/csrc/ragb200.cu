@@ -16,6 +16,7 @@
 #include "common.cuh"
 #include "gemm_topk.cuh"
 #include "gemm_ts.cuh"
+#include "gemm_pair.cuh"
 #include "ingest.cuh"
 #include "merge.cuh"
 #include "scan.cuh"
@@ -619,6 +620,74 @@ static int gemm_finish(ragb_store* s, const float* q, int64_t nq, int k, int kpa
   return merge_launch(tmp, nq, 1, kpad, kpad, kpad, k, out_scores, out_ids, out_keys, st, /*unsorted=*/true);
 }
 
+// SM-pair kernel (gemm_pair.cuh): tcgen05.mma.cta_group::2, M=256 (two query tiles) x N=256
+static int gemm_pair_search(ragb_store* s, const float* q, int64_t nq, int k, int metric, float threshold, int flags,
+                            int64_t rb, int64_t re, const uint8_t* valid, uint32_t id_base, uint64_t* out_keys,
+                            float* out_scores, int64_t* out_ids, cudaStream_t st) {
+  GemmState* g = &s->gemm;
+  const int kpad = kpad_of(k);
+  const int n_kb = (s->dim + kGemmKB - 1) / kGemmKB;
+  int n_qt = (int)((nq + kGemmM - 1) / kGemmM);
+  if (n_qt < 2) return RAGB_EUNSUPPORTED;
+  n_qt += n_qt & 1;  // an odd tile count gets one all-zero query tile
+  const int64_t nq_pad = (int64_t)n_qt * kGemmM;
+  if (g->pair_rows != s->rows || g->pair_capacity != s->capacity) {
+    RB_TRY(make_map(g, &g->map_x_pair, s->dtype, s->rows, s->dim, s->capacity, s->ld, kPairN / 2));
+    g->pair_rows = s->rows; g->pair_capacity = s->capacity;
+  }
+  RB_TRY(grow(&g->qh, &g->qh_bytes, (size_t)nq_pad * s->ld * 2, false));
+  if (s->dtype == RAGB_BF16)
+    convert_queries_kernel<__nv_bfloat16><<<(unsigned)(nq_pad / 4), 128, 0, st>>>(q, nq, s->dim, s->ld, metric, (__nv_bfloat16*)g->qh);
+  else
+    convert_queries_kernel<__half><<<(unsigned)(nq_pad / 4), 128, 0, st>>>(q, nq, s->dim, s->ld, metric, (__half*)g->qh);
+  LAUNCHED();
+  CUtensorMap map_q;
+  RB_TRY(make_map(g, &map_q, s->dtype, g->qh, s->dim, nq_pad, s->ld, kGemmM));
+  const size_t smem = 1024 + (size_t)kPairStages * kPairStageBytes + (size_t)kGemmM * kTsCandStride * 8 +
+                      (2 * kPairStages + 4) * 8 + 16;
+  static bool attr_set = false;
+  if (!attr_set) {
+    CU_TRY(cudaFuncSetAttribute(gemm_topk_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    attr_set = true;
+  }
+  cudaLaunchConfig_t cfg = {};
+  cudaLaunchAttribute attr[1];
+  cfg.blockDim = dim3(kGemmThreads); cfg.dynamicSmemBytes = smem; cfg.stream = st;
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr; cfg.numAttrs = 1;
+  if (g->pair_clusters == 0) {
+    cfg.gridDim = dim3((unsigned)(2 * (s->n_sm / 2)));
+    int nc = 0;
+    CU_TRY(cudaOccupancyMaxActiveClusters(&nc, gemm_topk_pair_kernel, &cfg));
+    g->pair_clusters = nc > 0 ? nc : s->n_sm / 2;
+  }
+  const int pps = n_qt / 2;
+  TsParams p = {};
+  p.qh = g->qh; p.ld_q = s->ld; p.n_kb = n_kb; p.nt = kPairN; p.kbs = 1; p.stages = kPairStages; p.cluster = 2;
+  p.row_begin = rb; p.row_end = re; p.valid = valid; p.nq = nq; p.n_qt = n_qt;
+  p.n_tiles = (re - rb + kPairN - 1) / kPairN;
+  int splits = std::max(1, g->pair_clusters / pps);
+  if (splits > p.n_tiles) splits = (int)p.n_tiles;
+  p.n_splits = splits;
+  const int k_sel = (flags & RAGB_NO_RESCORE) ? k : kpad;
+  p.flags = flags; p.threshold = threshold; p.k = k_sel; p.kpad = kpad;
+  p.id_base = id_base; p.idesc = umma_idesc(s->dtype == RAGB_BF16, 2 * kGemmM, kPairN);
+  const size_t part_bytes = (size_t)nq_pad * splits * kpad * sizeof(uint64_t);
+  const size_t tmp_bytes = (size_t)nq * kpad * sizeof(uint64_t);
+  RB_TRY(grow(&s->ws, &s->ws_bytes, part_bytes + tmp_bytes, false));
+  p.out = (uint64_t*)s->ws;
+  uint64_t* tmp = (uint64_t*)((char*)s->ws + part_bytes);
+  cfg.gridDim = dim3((unsigned)(n_qt * splits));
+  {
+    ProfScope prof(s, st);
+    CU_TRY(cudaLaunchKernelEx(&cfg, gemm_topk_pair_kernel, map_q, g->map_x_pair, p));
+  }
+  LAUNCHED();
+  return gemm_finish(s, q, nq, k, kpad, metric, threshold, flags, id_base, p.out, splits, tmp, out_keys, out_scores,
+                     out_ids, st, k_sel);
+}
+
 // query-stationary tcgen05 kernel (gemm_ts.cuh); returns RAGB_EUNSUPPORTED when the shape does not fit
 static int gemm_ts_search(ragb_store* s, const float* q, int64_t nq, int k, int metric, float threshold, int flags,
                           int64_t rb, int64_t re, const uint8_t* valid, uint32_t id_base, uint64_t* out_keys,
@@ -722,6 +791,10 @@ static int gemm_ts_search(ragb_store* s, const float* q, int64_t nq, int k, int 
 static int gemm_search(ragb_store* s, const float* q, int64_t nq, int k, int metric, float threshold, int flags,
                        int64_t rb, int64_t re, const uint8_t* valid, uint32_t id_base, uint64_t* out_keys,
                        float* out_scores, int64_t* out_ids, cudaStream_t st) {
+  if (env_int("RAGB_PAIR", 1) && !env_int("RAGB_GEMM_SS", 0) && !env_int("RAGB_TS", 0)) {
+    int r = gemm_pair_search(s, q, nq, k, metric, threshold, flags, rb, re, valid, id_base, out_keys, out_scores, out_ids, st);
+    if (r != RAGB_EUNSUPPORTED) return r;
+  }
   if (!env_int("RAGB_GEMM_SS", 0)) {
     int r = gemm_ts_search(s, q, nq, k, metric, threshold, flags, rb, re, valid, id_base, out_keys, out_scores, out_ids, st);
     if (r != RAGB_EUNSUPPORTED) return r;

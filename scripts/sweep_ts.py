@@ -23,6 +23,12 @@ def run(n, d, nq, envs, iters=5):
 
 if __name__ == "__main__":
     which = sys.argv[1] if len(sys.argv) > 1 else "a"
+    if which == "p":
+        for n, d in ((4_000_000, 768), (1_000_000, 384)):
+            run(n, d, 1024, [dict(RAGB_PAIR=1), dict(RAGB_PAIR=0)], iters=10)
+        run(4_000_000, 768, 4096, [dict(RAGB_PAIR=1), dict(RAGB_PAIR=0)], iters=3)
+        for b in (130, 200, 384, 640):
+            run(4_000_000, 768, b, [dict(RAGB_PAIR=1), dict(RAGB_PAIR=0)], iters=5)
     if which == "e":
         run(4_000_000, 768, 1024, [dict(RAGB_TS_NT=nt, RAGB_TS_KBS=kbs, RAGB_TS_CLUSTER=1) for nt, kbs in ((128, 1), (128, 2), (128, 3), (64, 1), (64, 2), (64, 4), (64, 6))])
     if which == "d":
