@@ -328,7 +328,8 @@ def run_b200(args):
     work = 2.0 * B * (r1 - r0) * d if tensor_path else float(r1 - r0) * d * 2
     roof = roofline_obj("tensor" if tensor_path else "hbm", store, torch, step, max(3, min(args.steps, 10)), work,
                         pk, pk_src, sustained=(ms / args.steps > 50.0))
-    roof["kernel"] = "gemm_topk_ts_kernel<false> (tcgen05 + TMA multicast)" if tensor_path else "scan_topk_kernel"
+    roof["kernel"] = ("gemm_topk_pair_kernel (tcgen05.mma cta_group::2 + TMA, fused top-k)" if tensor_path
+                      else "scan_topk_kernel")
     try:
         tr = json.loads((ROOT / "profiles" / "traffic.json").read_text()).get(f"{args.workload}_b{B}_n{world}")
         if tr:

@@ -23,7 +23,8 @@
 
 namespace ragb {
 
-constexpr int kPairStages = 5;
+constexpr int kPairStagesSmall = 5;              // ring depth next to the shared-memory candidate buffers (kpad <= 32)
+constexpr int kPairStagesLarge = 6;              // kpad 64 / 128: candidates live in global memory
 constexpr int kPairN = 256;                       // corpus rows per accumulator tile (both halves)
 constexpr int kPairStageBytes = 2 * kStageBytesA; // 16 KB queries + 16 KB half corpus tile
 constexpr uint32_t kPeerBitMask = 0xFEFFFFFFu;    // shared::cluster address of the even (leader) CTA of a pair
@@ -68,53 +69,148 @@ __device__ __forceinline__ void mbar_wait_cluster(uint64_t* bar, uint32_t parity
       "DONEC_%=:\n\t}" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
 }
 
-// ---- the fused top-k epilogue on one 32-column chunk (shared with nothing else yet) -----------
-struct EpiCtx {
-  uint64_t* my;         // this query's candidate buffer
-  uint64_t* warp_cand;  // buffer of lane 0 of this warp
-  int cnt;
-  float user_fast, fthr;
+// ---- candidate buffers ----------------------------------------------------------------------
+// E selects the per-query candidate buffer:
+//   E == 2 : kpad <= 32, 48 slots in shared memory, pruned by warp_top32_of_64
+//   E == 4 : kpad == 64, E == 8 : kpad == 128 — 32*E slots in GLOBAL memory (L2 resident; an insert is a rare
+//            event, about k*ln(rows/k) per query over a CTA's lifetime), pruned by a register bitonic sort
+constexpr int kPairCapSmall = 64;
+template <int E> struct CandCfg {
+  static constexpr int cap = E == 2 ? kPairCapSmall : 32 * E;
+  static constexpr int stride = E == 2 ? kPairCapSmall + 1 : 32 * E;  // +1: conflict-free for both access patterns
 };
-__device__ __forceinline__ void epi_chunk(EpiCtx& e, const uint32_t (&r)[32], int64_t row_c, const TsParams& p, int lane) {
-  float m[4];
+constexpr int kChunkRows = 32;  // rows behind one candidate key (one tcgen05.ld of 32 columns)
+
+__device__ __forceinline__ float fmax3(float a, float b, float c) {
+  float r;
+  asm("max.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c));
+  return r;
+}
+// tcgen05.wait::ld that also redefines the registers of the load it waits for, so that no use of them
+// can be scheduled above it
+__device__ __forceinline__ void tc_wait_ld_dep(uint32_t* r) {
+  asm volatile("tcgen05.wait::ld.sync.aligned;"
+               : "+r"(r[0]), "+r"(r[1]), "+r"(r[2]), "+r"(r[3]), "+r"(r[4]), "+r"(r[5]), "+r"(r[6]), "+r"(r[7]),
+                 "+r"(r[8]), "+r"(r[9]), "+r"(r[10]), "+r"(r[11]), "+r"(r[12]), "+r"(r[13]), "+r"(r[14]), "+r"(r[15]),
+                 "+r"(r[16]), "+r"(r[17]), "+r"(r[18]), "+r"(r[19]), "+r"(r[20]), "+r"(r[21]), "+r"(r[22]), "+r"(r[23]),
+                 "+r"(r[24]), "+r"(r[25]), "+r"(r[26]), "+r"(r[27]), "+r"(r[28]), "+r"(r[29]), "+r"(r[30]), "+r"(r[31])
+               :
+               : "memory");
+}
+
+// bitonic sort of 32*E keys held E per lane (element index i = e*32 + lane), descending in i
+template <int E>
+__device__ __forceinline__ void warp_sort_desc(uint64_t (&v)[E], int lane) {
 #pragma unroll
-  for (int g = 0; g < 4; ++g) {
-    float a = fmaxf(__uint_as_float(r[8 * g]), __uint_as_float(r[8 * g + 1]));
-    float b = fmaxf(__uint_as_float(r[8 * g + 2]), __uint_as_float(r[8 * g + 3]));
-    float c = fmaxf(__uint_as_float(r[8 * g + 4]), __uint_as_float(r[8 * g + 5]));
-    float d = fmaxf(__uint_as_float(r[8 * g + 6]), __uint_as_float(r[8 * g + 7]));
-    m[g] = fmaxf(fmaxf(a, b), fmaxf(c, d));
-  }
-  const float mx = fmaxf(fmaxf(m[0], m[1]), fmaxf(m[2], m[3]));
-  if (!__any_sync(0xffffffffu, mx >= e.fthr)) return;
+  for (int size = 2; size <= 32 * E; size <<= 1) {
 #pragma unroll
-  for (int g = 0; g < 4; ++g) {
-    if (__any_sync(0xffffffffu, m[g] >= e.fthr)) {
+    for (int stride = size >> 1; stride > 0; stride >>= 1) {
+      if (stride >= 32) {
+        const int se = stride >> 5;
 #pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        const float raw = __uint_as_float(r[8 * g + j]);
-        if (raw >= e.fthr) {
-          const int64_t row = row_c + g * 8 + j;
-          const float sc = finish_score(raw, 1.0f, p.flags);
-          bool ok = row < p.row_end && sc >= p.threshold;
-          if (ok && p.valid) ok = p.valid[row] != 0;
-          if (ok) e.my[e.cnt++] = make_key(sc, (uint32_t)row + p.id_base);
+        for (int e = 0; e < E; ++e) {
+          if ((e & se) == 0) {
+            const bool desc = ((e << 5) & size) == 0;
+            const uint64_t a = v[e], b = v[e | se];
+            const uint64_t hi = a > b ? a : b, lo = a > b ? b : a;
+            v[e] = desc ? hi : lo;
+            v[e | se] = desc ? lo : hi;
+          }
+        }
+      } else {
+        const bool lower = (lane & stride) == 0;
+#pragma unroll
+        for (int e = 0; e < E; ++e) {
+          const uint64_t o = __shfl_xor_sync(0xffffffffu, v[e], stride);
+          const bool desc = (((e << 5) | lane) & size) == 0;
+          const bool take_max = lower == desc;
+          v[e] = take_max ? (v[e] > o ? v[e] : o) : (v[e] < o ? v[e] : o);
         }
       }
     }
   }
-  // a chunk adds at most 32: pruning whenever more than 32 are held keeps cnt <= 64
-  unsigned need = __ballot_sync(0xffffffffu, e.cnt > kTsCap - 32);
+}
+
+// All 32 lanes: sort the n keys of one query's buffer, keep the best min(n,k) in place (sorted),
+// return the k-th best (0 if fewer than k are held).
+template <int E>
+__device__ __forceinline__ uint64_t warp_prune(uint64_t* base, int n, int k, int lane, int* keep_out) {
+  const int keep = n < k ? n : k;
+  *keep_out = keep;
+  if constexpr (E == 2) {
+    const uint64_t v = warp_top32_of_64(base, n, lane);
+    __syncwarp();
+    if (lane < keep) base[lane] = v;
+    return __shfl_sync(0xffffffffu, v, k - 1);
+  } else {
+    uint64_t v[E];
+#pragma unroll
+    for (int e = 0; e < E; ++e) v[e] = (e * 32 + lane < n) ? base[e * 32 + lane] : 0ull;
+    warp_sort_desc<E>(v, lane);
+    __syncwarp();
+    uint64_t kv = 0;
+#pragma unroll
+    for (int e = 0; e < E; ++e) {
+      if (e * 32 + lane < keep) base[e * 32 + lane] = v[e];
+      if (e == ((k - 1) >> 5)) kv = v[e];
+    }
+    return __shfl_sync(0xffffffffu, kv, (k - 1) & 31);
+  }
+}
+
+// ---- the fused top-k epilogue: CHUNK-granular selection -----------------------------------------
+// Thread == query holds the scores of its query against 32 consecutive rows (one chunk).  The epilogue
+// keeps, per query, the best k_sel CHUNKS ranked by (chunk maximum, chunk start row): a 3-input max
+// tree and one compare per chunk, and — rarely, about k*ln(chunks/k) times per query — one store.
+// Why that is exact: the k best rows of a query lie inside its k best chunks.  (A chunk outside them
+// is beaten by k chunks whose maximum rows each beat every row of it — by score, or on equal score by
+// the larger row id, since a later chunk holds later rows.)  The k-th best chunk maximum is therefore
+// also a valid running threshold.  rescore_chunks_kernel then scores the 32 rows of every selected
+// chunk in fp32 and the merge keeps the k best rows; row range, valid mask and the user threshold are
+// applied there, exactly.  Here rows outside the range / masked out are only kept from raising a
+// chunk's maximum (kMasked), so the threshold stays a lower bound.
+struct EpiCtx {
+  uint64_t* my;         // this query's candidate buffer
+  uint64_t* warp_cand;  // buffer of lane 0 of this warp; lane j's is warp_cand + j*stride
+  int cnt;
+  float user_fast, fthr;
+};
+template <bool kMasked>
+__device__ __forceinline__ void epi_chunk(EpiCtx& e, uint32_t (&r)[32], int64_t row_c, const TsParams& p, int lane) {
+  bool any_row = true;
+  if (kMasked) {
+    const int64_t row = row_c + lane;
+    bool v = row < p.row_end;
+    if (v && p.valid) v = p.valid[row] != 0;
+    const unsigned vb = __ballot_sync(0xffffffffu, v);
+    any_row = vb != 0;
+    if (vb != 0xffffffffu) {
+#pragma unroll
+      for (int j = 0; j < 32; ++j)
+        if (!((vb >> j) & 1u)) r[j] = 0xff800000u;  // -inf: cannot raise the chunk maximum
+    }
+  }
+  float t[11];
+#pragma unroll
+  for (int i = 0; i < 10; ++i)
+    t[i] = fmax3(__uint_as_float(r[3 * i]), __uint_as_float(r[3 * i + 1]), __uint_as_float(r[3 * i + 2]));
+  t[10] = fmaxf(__uint_as_float(r[30]), __uint_as_float(r[31]));
+  const float u0 = fmax3(t[0], t[1], t[2]), u1 = fmax3(t[3], t[4], t[5]), u2 = fmax3(t[6], t[7], t[8]);
+  const float mx = fmax3(fmax3(u0, u1, u2), t[9], t[10]);
+  if (mx >= e.fthr && any_row) e.my[e.cnt++] = make_key(finish_score(mx, 1.0f, p.flags), (uint32_t)row_c);
+}
+// once per tile (a query gains at most 8 chunks per tile): prune the buffers that could overflow next tile
+template <int E>
+__device__ __forceinline__ void epi_prune(EpiCtx& e, const TsParams& p, int lane) {
+  constexpr int kCap = CandCfg<E>::cap, kStride = CandCfg<E>::stride;
+  unsigned need = __ballot_sync(0xffffffffu, e.cnt > kCap - kPairN / kChunkRows);
   while (need) {
     const int j = __ffs(need) - 1;
     need &= need - 1;
     const int n = __shfl_sync(0xffffffffu, e.cnt, j);
     __syncwarp();
-    const uint64_t v = warp_top32_of_64(e.warp_cand + (size_t)j * kTsCandStride, n, lane);
-    const int keep = n < p.k ? n : p.k;
-    __syncwarp();
-    if (lane < keep) e.warp_cand[(size_t)j * kTsCandStride + lane] = v;
-    const uint64_t kth = __shfl_sync(0xffffffffu, v, p.k - 1);
+    int keep;
+    const uint64_t kth = warp_prune<E>(e.warp_cand + (size_t)j * kStride, n, p.k, lane, &keep);
     if (lane == j) {
       e.cnt = keep;
       if (n >= p.k) e.fthr = fmaxf(e.user_fast, fast_bound(key_score(kth), p.flags));
@@ -122,17 +218,31 @@ __device__ __forceinline__ void epi_chunk(EpiCtx& e, const uint32_t (&r)[32], in
     __syncwarp();
   }
 }
-// sort every query's survivors and write kpad keys (kpad <= 32)
+// sort every query's survivors and write kpad keys
+template <int E>
 __device__ __forceinline__ void epi_flush(EpiCtx& e, int64_t qrow0, int split, const TsParams& p, int lane) {
+  constexpr int kStride = CandCfg<E>::stride;
   __syncwarp();
   for (int j = 0; j < 32; ++j) {
     const int n = __shfl_sync(0xffffffffu, e.cnt, j);
-    const uint64_t v = warp_top32_of_64(e.warp_cand + (size_t)j * kTsCandStride, n, lane);
+    uint64_t* base = e.warp_cand + (size_t)j * kStride;
+    uint64_t* out = p.out + ((size_t)(qrow0 + j) * p.n_splits + split) * p.kpad;
     const int keep = n < p.k ? n : p.k;
-    if (lane < p.kpad) p.out[((size_t)(qrow0 + j) * p.n_splits + split) * p.kpad + lane] = lane < keep ? v : 0ull;
+    if constexpr (E == 2) {
+      const uint64_t v = warp_top32_of_64(base, n, lane);
+      if (lane < p.kpad) out[lane] = lane < keep ? v : 0ull;
+    } else {
+      uint64_t v[E];
+#pragma unroll
+      for (int x = 0; x < E; ++x) v[x] = (x * 32 + lane < n) ? base[x * 32 + lane] : 0ull;
+      warp_sort_desc<E>(v, lane);
+#pragma unroll
+      for (int x = 0; x < E / 2; ++x) out[x * 32 + lane] = (x * 32 + lane < keep) ? v[x] : 0ull;
+    }
   }
 }
 
+template <int E, int kPairStages>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_x,
                       const TsParams p) {
@@ -140,8 +250,9 @@ gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_co
   // carve: stages | candidate buffers | barriers | tmem base     (identical offsets in both CTAs)
   uint8_t* smem = reinterpret_cast<uint8_t*>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   uint8_t* stage_base = smem;
-  uint64_t* cand = reinterpret_cast<uint64_t*>(smem + (size_t)kPairStages * kPairStageBytes);
-  uint64_t* bars = cand + (size_t)kGemmM * kTsCandStride;
+  uint64_t* cand_smem = reinterpret_cast<uint64_t*>(smem + (size_t)kPairStages * kPairStageBytes);
+  uint64_t* bars = cand_smem + (E == 2 ? (size_t)kGemmM * CandCfg<E>::stride : 0);
+  uint64_t* cand = E == 2 ? cand_smem : p.cand_ws + (size_t)blockIdx.x * kGemmM * CandCfg<E>::stride;
   uint64_t* full_bar = bars;                     // leader's copy is the one in use
   uint64_t* empty_bar = bars + kPairStages;      // one per CTA
   uint64_t* tfull_bar = bars + 2 * kPairStages;  // one per CTA
@@ -223,11 +334,12 @@ gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_co
     const int tid = quarter * 32 + lane;
     const uint32_t lane_base = tmem_base + ((uint32_t)(quarter * 32) << 16);
     EpiCtx e;
-    e.my = cand + (size_t)tid * kTsCandStride;
-    e.warp_cand = cand + (size_t)(quarter * 32) * kTsCandStride;
+    e.my = cand + (size_t)tid * CandCfg<E>::stride;
+    e.warp_cand = cand + (size_t)(quarter * 32) * CandCfg<E>::stride;
     e.cnt = 0;
     // rows of the query tile past nq are zero padding: they must never take the candidate path
-    e.user_fast = ((int64_t)qt * kGemmM + tid < p.nq) ? fast_bound(p.threshold, p.flags) : INFINITY;
+    // the 16-bit-query scores only SELECT: the user threshold is applied with slack here, exactly by the re-score
+    e.user_fast = ((int64_t)qt * kGemmM + tid < p.nq) ? fast_bound(p.threshold - p.sel_slack, p.flags) : INFINITY;
     e.fthr = e.user_fast;
     uint32_t acc = 0, aph = 0;
     for (int64_t t = t0; t < t1; ++t) {
@@ -235,19 +347,37 @@ gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_co
       mbar_wait(&tfull_bar[acc], aph);
       tc_fence_after();
       const uint32_t taddr = lane_base + acc * (uint32_t)kPairN;
+      // two register sets: the TMEM load of the next 32 columns is in flight while this one is examined
+      uint32_t ra[32], rb[32];
+      tc_ld32(taddr, ra);
+      if (p.valid == nullptr && row0 + kPairN <= p.row_end) {
 #pragma unroll 1
-      for (int c = 0; c < kPairN / 32; ++c) {
-        uint32_t r[32];
-        tc_ld32(taddr + c * 32, r);
-        tc_wait_ld();
-        epi_chunk(e, r, row0 + c * 32, p, lane);
+        for (int c = 0; c < kPairN / 32; c += 2) {
+          tc_wait_ld_dep(ra);
+          tc_ld32(taddr + (c + 1) * 32, rb);
+          epi_chunk<false>(e, ra, row0 + c * 32, p, lane);
+          tc_wait_ld_dep(rb);
+          if (c + 2 < kPairN / 32) tc_ld32(taddr + (c + 2) * 32, ra);
+          epi_chunk<false>(e, rb, row0 + (c + 1) * 32, p, lane);
+        }
+      } else {  // valid mask given, or the tile reaches past row_end
+#pragma unroll 1
+        for (int c = 0; c < kPairN / 32; c += 2) {
+          tc_wait_ld_dep(ra);
+          tc_ld32(taddr + (c + 1) * 32, rb);
+          epi_chunk<true>(e, ra, row0 + c * 32, p, lane);
+          tc_wait_ld_dep(rb);
+          if (c + 2 < kPairN / 32) tc_ld32(taddr + (c + 2) * 32, ra);
+          epi_chunk<true>(e, rb, row0 + (c + 1) * 32, p, lane);
+        }
       }
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive_cta(&tempty_bar[acc], 0);
       if ((acc ^= 1) == 0) aph ^= 1;
+      epi_prune<E>(e, p, lane);  // after the accumulator is handed back: off the MMA's critical path
     }
-    epi_flush(e, (int64_t)qt * kGemmM + quarter * 32, split, p, lane);
+    epi_flush<E>(e, (int64_t)qt * kGemmM + quarter * 32, split, p, lane);
   }
 
   tc_fence_before();

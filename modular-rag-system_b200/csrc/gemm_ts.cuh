@@ -51,6 +51,8 @@ struct TsParams {
   int k, kpad;
   uint32_t id_base, idesc;
   uint64_t* out;        // [n_qt*128][n_splits][kpad] sorted keys
+  uint64_t* cand_ws;    // pair kernel, kpad > 32: [grid][128][2*kpad] candidate buffers in global memory
+  float sel_slack;      // pair kernel: slack under the user threshold for the 16-bit-query selection pass
 };
 
 __device__ __forceinline__ void tma_load_2d_mc(void* dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1,

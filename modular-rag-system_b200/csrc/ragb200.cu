@@ -61,6 +61,8 @@ static size_t elem_size(int dtype) { return dtype == RAGB_F32 ? 4 : 2; }
 // ---------------------------------------------------------------------------
 // store
 // ---------------------------------------------------------------------------
+constexpr int64_t kScanMaxQ = 65535;  // grid y limit of one scan launch
+
 struct ragb_store {
   int device = 0, dim = 0, dtype = 0, n_sm = 148;
   int64_t ld = 0, capacity = 0;
@@ -72,6 +74,7 @@ struct ragb_store {
   // search workspace (guarded by search_mu)
   void* ws = nullptr;
   size_t ws_bytes = 0;
+  unsigned* tickets = nullptr;  // [kScanMaxQ] zero between launches: last-CTA final merge of the scan (scan.cuh)
   // ingest staging (guarded by add_mu)
   void* stage_dev = nullptr;
   size_t stage_dev_bytes = 0;
@@ -171,6 +174,9 @@ extern "C" int ragb_store_create(int device, int dim, int dtype, int64_t capacit
   if (r != RAGB_OK) { delete s; return r; }
   e = cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking);
   if (e != cudaSuccess) { cudaFree(s->rows); cudaFree(s->norms); delete s; return fail(RAGB_ECUDA, "cudaStreamCreate: %s", cudaGetErrorString(e)); }
+  e = cudaMalloc(&s->tickets, kScanMaxQ * sizeof(unsigned));
+  if (e != cudaSuccess) { cudaStreamDestroy(s->stream); cudaFree(s->rows); cudaFree(s->norms); delete s; return fail(RAGB_ENOMEM, "cudaMalloc tickets: %s", cudaGetErrorString(e)); }
+  cudaMemsetAsync(s->tickets, 0, kScanMaxQ * sizeof(unsigned), s->stream);
   // padding columns must read as zero
   cudaMemsetAsync(s->rows, 0, (size_t)capacity * s->ld * elem_size(dtype), s->stream);
   cudaStreamSynchronize(s->stream);
@@ -184,7 +190,7 @@ extern "C" int ragb_store_destroy(ragb_store* s) {
     DeviceGuard g(s->device);
     cudaStreamSynchronize(s->stream);
     gemm_state_free(&s->gemm);
-    cudaFree(s->rows); cudaFree(s->norms); cudaFree(s->ws); cudaFree(s->stage_dev); cudaFree(s->io);
+    cudaFree(s->rows); cudaFree(s->norms); cudaFree(s->ws); cudaFree(s->stage_dev); cudaFree(s->io); cudaFree(s->tickets);
     if (s->stage_host) cudaFreeHost(s->stage_host);
     if (s->pin) cudaFreeHost(s->pin);
     for (auto& ev : s->prof_events) { cudaEventDestroy(ev.first); cudaEventDestroy(ev.second); }
@@ -587,8 +593,17 @@ static int make_map(GemmState* g, CUtensorMap* map, int dtype, const void* base,
   return RAGB_OK;
 }
 
+static int env_int(const char* name, int dflt) {
+  const char* v = getenv(name);
+  return (v && *v) ? atoi(v) : dflt;
+}
+static bool pair_enabled() { return env_int("RAGB_PAIR", 1) && !env_int("RAGB_GEMM_SS", 0) && !env_int("RAGB_TS", 0); }
+
 static bool gemm_eligible(const ragb_store* s, int64_t nq, int k, int flags) {
-  if (s->dtype == RAGB_F32 || kpad_of(k) > kGemmMaxKpad || (flags & RAGB_FORCE_SCAN)) return false;
+  if (s->dtype == RAGB_F32 || (flags & RAGB_FORCE_SCAN)) return false;
+  const int kp = kpad_of(k);
+  // kpad 64 / 128 exists only in the SM-pair kernel (needs two 128-query tiles)
+  if (kp > kGemmMaxKpad) return kp <= 128 && nq > kGemmM && pair_enabled() && !(flags & RAGB_NO_RESCORE);
   return (flags & RAGB_FORCE_GEMM) || nq >= 4;
 }
 
@@ -600,11 +615,6 @@ static int rescore_launch(ragb_store* s, const float* q, int64_t nq, int metric,
                                                                 threshold, id_base, kpad, keys);
   LAUNCHED();
   return RAGB_OK;
-}
-
-static int env_int(const char* name, int dflt) {
-  const char* v = getenv(name);
-  return (v && *v) ? atoi(v) : dflt;
 }
 
 // merge the per-split lists, optionally re-score the winners in fp32, decode
@@ -620,6 +630,26 @@ static int gemm_finish(ragb_store* s, const float* q, int64_t nq, int k, int kpa
   return merge_launch(tmp, nq, 1, kpad, kpad, kpad, k, out_scores, out_ids, out_keys, st, /*unsorted=*/true);
 }
 
+// SM-pair kernel epilogue: merge the per-split CHUNK lists, score the 32 rows of every selected chunk in fp32,
+// keep the k best rows
+static int gemm_finish_chunks(ragb_store* s, const float* q, int64_t nq, int k, int kpad, int k_sel, int metric,
+                              float threshold, int flags, int64_t rb, int64_t re, const uint8_t* valid, uint32_t id_base,
+                              const uint64_t* parts, int splits, uint64_t* tmp, uint64_t* tmp_rows, uint64_t* out_keys,
+                              float* out_scores, int64_t* out_ids, cudaStream_t st) {
+  RB_TRY(merge_launch(parts, nq, splits, kpad, (int64_t)splits * kpad, kpad, k_sel, nullptr, nullptr, tmp, st));
+  const int64_t warps = nq * kpad;
+  const unsigned grid = (unsigned)((warps + 7) / 8);
+  if (s->dtype == RAGB_BF16)
+    rescore_chunks_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>((const __nv_bfloat16*)s->rows, s->ld, s->dim, q, nq, metric, flags,
+                                                              threshold, rb, re, valid, id_base, kpad, tmp, tmp_rows);
+  else
+    rescore_chunks_kernel<__half><<<grid, 256, 0, st>>>((const __half*)s->rows, s->ld, s->dim, q, nq, metric, flags, threshold,
+                                                       rb, re, valid, id_base, kpad, tmp, tmp_rows);
+  LAUNCHED();
+  return merge_launch(tmp_rows, nq, kChunkRows, kpad, (int64_t)kChunkRows * kpad, kpad, k, out_scores, out_ids, out_keys, st,
+                      /*unsorted=*/true);
+}
+
 // SM-pair kernel (gemm_pair.cuh): tcgen05.mma.cta_group::2, M=256 (two query tiles) x N=256
 static int gemm_pair_search(ragb_store* s, const float* q, int64_t nq, int k, int metric, float threshold, int flags,
                             int64_t rb, int64_t re, const uint8_t* valid, uint32_t id_base, uint64_t* out_keys,
@@ -628,7 +658,8 @@ static int gemm_pair_search(ragb_store* s, const float* q, int64_t nq, int k, in
   const int kpad = kpad_of(k);
   const int n_kb = (s->dim + kGemmKB - 1) / kGemmKB;
   int n_qt = (int)((nq + kGemmM - 1) / kGemmM);
-  if (n_qt < 2) return RAGB_EUNSUPPORTED;
+  // the pair kernel selects CHUNKS of 32 rows; the fp32 re-score resolves them to rows, so it cannot be skipped
+  if (n_qt < 2 || (flags & RAGB_NO_RESCORE)) return RAGB_EUNSUPPORTED;
   n_qt += n_qt & 1;  // an odd tile count gets one all-zero query tile
   const int64_t nq_pad = (int64_t)n_qt * kGemmM;
   if (g->pair_rows != s->rows || g->pair_capacity != s->capacity) {
@@ -643,12 +674,20 @@ static int gemm_pair_search(ragb_store* s, const float* q, int64_t nq, int k, in
   LAUNCHED();
   CUtensorMap map_q;
   RB_TRY(make_map(g, &map_q, s->dtype, g->qh, s->dim, nq_pad, s->ld, kGemmM));
-  const size_t smem = 1024 + (size_t)kPairStages * kPairStageBytes + (size_t)kGemmM * kTsCandStride * 8 +
-                      (2 * kPairStages + 4) * 8 + 16;
-  static bool attr_set = false;
-  if (!attr_set) {
-    CU_TRY(cudaFuncSetAttribute(gemm_topk_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    attr_set = true;
+  // kpad <= 32: candidate buffers in shared memory, 5-stage ring; kpad 64 / 128: buffers in global memory, 6 stages
+  const int E = kpad <= 32 ? 2 : kpad == 64 ? 4 : 8;
+  if (kpad > 128) return RAGB_EUNSUPPORTED;
+  const int n_stages = E == 2 ? kPairStagesSmall : kPairStagesLarge;
+  const size_t smem = 1024 + (size_t)n_stages * kPairStageBytes + (E == 2 ? (size_t)kGemmM * (kPairCapSmall + 1) * 8 : 0) +
+                      (2 * n_stages + 4) * 8 + 16;
+  typedef void (*PairKernel)(const CUtensorMap, const CUtensorMap, const TsParams);
+  PairKernel kern = E == 2 ? gemm_topk_pair_kernel<2, kPairStagesSmall>
+                  : E == 4 ? gemm_topk_pair_kernel<4, kPairStagesLarge> : gemm_topk_pair_kernel<8, kPairStagesLarge>;
+  const int ei = E == 2 ? 0 : E == 4 ? 1 : 2;
+  static bool attr_set[3] = {false, false, false};
+  if (!attr_set[ei]) {
+    CU_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    attr_set[ei] = true;
   }
   cudaLaunchConfig_t cfg = {};
   cudaLaunchAttribute attr[1];
@@ -656,36 +695,42 @@ static int gemm_pair_search(ragb_store* s, const float* q, int64_t nq, int k, in
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr; cfg.numAttrs = 1;
-  if (g->pair_clusters == 0) {
+  if (g->pair_clusters[ei] == 0) {
     cfg.gridDim = dim3((unsigned)(2 * (s->n_sm / 2)));
     int nc = 0;
-    CU_TRY(cudaOccupancyMaxActiveClusters(&nc, gemm_topk_pair_kernel, &cfg));
-    g->pair_clusters = nc > 0 ? nc : s->n_sm / 2;
+    CU_TRY(cudaOccupancyMaxActiveClusters(&nc, kern, &cfg));
+    g->pair_clusters[ei] = nc > 0 ? nc : s->n_sm / 2;
   }
   const int pps = n_qt / 2;
   TsParams p = {};
-  p.qh = g->qh; p.ld_q = s->ld; p.n_kb = n_kb; p.nt = kPairN; p.kbs = 1; p.stages = kPairStages; p.cluster = 2;
+  p.qh = g->qh; p.ld_q = s->ld; p.n_kb = n_kb; p.nt = kPairN; p.kbs = 1; p.stages = n_stages; p.cluster = 2;
   p.row_begin = rb; p.row_end = re; p.valid = valid; p.nq = nq; p.n_qt = n_qt;
   p.n_tiles = (re - rb + kPairN - 1) / kPairN;
-  int splits = std::max(1, g->pair_clusters / pps);
+  int splits = std::max(1, g->pair_clusters[ei] / pps);
   if (splits > p.n_tiles) splits = (int)p.n_tiles;
   p.n_splits = splits;
-  const int k_sel = (flags & RAGB_NO_RESCORE) ? k : kpad;
+  const int k_sel = kpad;  // chunks kept per query: >= k, the slack absorbs the rounding of the 16-bit queries
   p.flags = flags; p.threshold = threshold; p.k = k_sel; p.kpad = kpad;
-  p.id_base = id_base; p.idesc = umma_idesc(s->dtype == RAGB_BF16, 2 * kGemmM, kPairN);
+  p.sel_slack = s->dtype == RAGB_BF16 ? 8e-3f : 2e-3f;
+  p.id_base = 0;  // chunk keys carry LOCAL start rows; the re-score adds id_base
+  p.idesc = umma_idesc(s->dtype == RAGB_BF16, 2 * kGemmM, kPairN);
   const size_t part_bytes = (size_t)nq_pad * splits * kpad * sizeof(uint64_t);
   const size_t tmp_bytes = (size_t)nq * kpad * sizeof(uint64_t);
-  RB_TRY(grow(&s->ws, &s->ws_bytes, part_bytes + tmp_bytes, false));
+  const size_t rows_bytes = tmp_bytes * kChunkRows;
+  const size_t cand_bytes = E == 2 ? 0 : (size_t)n_qt * splits * kGemmM * (32 * E) * sizeof(uint64_t);
+  RB_TRY(grow(&s->ws, &s->ws_bytes, part_bytes + tmp_bytes + rows_bytes + cand_bytes, false));
   p.out = (uint64_t*)s->ws;
   uint64_t* tmp = (uint64_t*)((char*)s->ws + part_bytes);
+  uint64_t* tmp_rows = (uint64_t*)((char*)s->ws + part_bytes + tmp_bytes);
+  p.cand_ws = E == 2 ? nullptr : (uint64_t*)((char*)s->ws + part_bytes + tmp_bytes + rows_bytes);
   cfg.gridDim = dim3((unsigned)(n_qt * splits));
   {
     ProfScope prof(s, st);
-    CU_TRY(cudaLaunchKernelEx(&cfg, gemm_topk_pair_kernel, map_q, g->map_x_pair, p));
+    CU_TRY(cudaLaunchKernelEx(&cfg, kern, map_q, g->map_x_pair, p));
   }
   LAUNCHED();
-  return gemm_finish(s, q, nq, k, kpad, metric, threshold, flags, id_base, p.out, splits, tmp, out_keys, out_scores,
-                     out_ids, st, k_sel);
+  return gemm_finish_chunks(s, q, nq, k, kpad, k_sel, metric, threshold, flags, rb, re, valid, id_base, p.out, splits, tmp,
+                            tmp_rows, out_keys, out_scores, out_ids, st);
 }
 
 // query-stationary tcgen05 kernel (gemm_ts.cuh); returns RAGB_EUNSUPPORTED when the shape does not fit
@@ -791,7 +836,7 @@ static int gemm_ts_search(ragb_store* s, const float* q, int64_t nq, int k, int 
 static int gemm_search(ragb_store* s, const float* q, int64_t nq, int k, int metric, float threshold, int flags,
                        int64_t rb, int64_t re, const uint8_t* valid, uint32_t id_base, uint64_t* out_keys,
                        float* out_scores, int64_t* out_ids, cudaStream_t st) {
-  if (env_int("RAGB_PAIR", 1) && !env_int("RAGB_GEMM_SS", 0) && !env_int("RAGB_TS", 0)) {
+  if (pair_enabled()) {
     int r = gemm_pair_search(s, q, nq, k, metric, threshold, flags, rb, re, valid, id_base, out_keys, out_scores, out_ids, st);
     if (r != RAGB_EUNSUPPORTED) return r;
   }
@@ -872,22 +917,30 @@ static int search_core(ragb_store* s, const float* q, int64_t nq, int k, int met
   p.X = s->rows; p.ld = s->ld; p.dim = s->dim; p.row_begin = rb; p.row_end = re; p.valid = valid;
   p.q = q; p.ld_q = s->dim; p.metric = metric; p.flags = flags; p.threshold = threshold;
   p.k = k; p.kpad = kpad; p.id_base = id_base; p.out = nullptr;
+  p.tickets = nullptr; p.out_scores = nullptr; p.out_ids = nullptr; p.out_keys = nullptr;
   // the grid y dimension caps one launch at 65535 queries
   int n_lists = 0;
   RB_TRY(scan_launch(s->dtype, p, nq, s->n_sm, st, &n_lists));  // sizing
-  const int64_t q_step = 65535;
+  const int64_t q_step = kScanMaxQ;
   RB_TRY(grow(&s->ws, &s->ws_bytes, (size_t)std::min(nq, q_step) * n_lists * kpad * sizeof(uint64_t), false));
+  // one launch per <= 65535 queries: the last CTA of each query folds the per-CTA lists (RAGB_SCAN_2PASS=1
+  // brings the separate merge kernel back, for A/B timing)
+  const bool fused = !env_int("RAGB_SCAN_2PASS", 0);
   for (int64_t q0 = 0; q0 < nq; q0 += q_step) {
     const int64_t m = std::min(q_step, nq - q0);
     p.q = q + (size_t)q0 * s->dim;
     p.out = (uint64_t*)s->ws;
+    p.tickets = fused ? s->tickets : nullptr;
+    p.out_scores = out_scores ? out_scores + q0 * k : nullptr;
+    p.out_ids = out_ids ? out_ids + q0 * k : nullptr;
+    p.out_keys = out_keys ? out_keys + q0 * kpad : nullptr;
     {
       ProfScope prof(s, st);
       RB_TRY(scan_launch(s->dtype, p, m, s->n_sm, st, &n_lists));
     }
-    RB_TRY(merge_launch((const uint64_t*)s->ws, m, n_lists, kpad, (int64_t)n_lists * kpad, kpad, k,
-                        out_scores ? out_scores + q0 * k : nullptr, out_ids ? out_ids + q0 * k : nullptr,
-                        out_keys ? out_keys + q0 * kpad : nullptr, st));
+    if (!fused)
+      RB_TRY(merge_launch((const uint64_t*)s->ws, m, n_lists, kpad, (int64_t)n_lists * kpad, kpad, k, p.out_scores,
+                          p.out_ids, p.out_keys, st));
   }
   return RAGB_OK;
 }

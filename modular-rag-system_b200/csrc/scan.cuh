@@ -29,6 +29,11 @@ struct ScanParams {
   int k, kpad;
   uint32_t id_base;
   uint64_t* out;         // [nq][gridDim.x][kpad]
+  // fused final merge (the last CTA of a query to finish folds all per-CTA lists): null tickets = off
+  unsigned* tickets;     // [nq], zero before the launch; the merging CTA resets its entry
+  float* out_scores;     // [nq][k] or null
+  int64_t* out_ids;      // [nq][k] or null
+  uint64_t* out_keys;    // [nq][kpad] or null (sorted keys, for the cross-GPU merge)
 };
 
 __device__ __forceinline__ float query_scale(const float* q, int dim, int metric, int lane) {
@@ -49,8 +54,51 @@ __device__ __forceinline__ void cta_reduce_and_store(WarpTopK& tk, uint64_t* sme
       tk.merge_list(smem_lists + (size_t)(warp + s) * tk.len, lane);
     __syncthreads();
   }
-  if (warp == 0)
+  if (warp == 0) {
     for (int i = lane; i < tk.kpad; i += 32) out[i] = tk.buf[i];
+    __threadfence();  // the list must be visible before this CTA takes its ticket
+  }
+}
+
+// The reference's final "sorted(...)[:max_results]" (ollama_rag_system.py:511-515) without a second
+// launch: every CTA takes a ticket after its list is in global memory; the CTA that draws the last
+// ticket of its query reads all gridDim.x lists back (L2), folds them and decodes the k winners.
+__device__ __forceinline__ void fused_final_merge(WarpTopK& tk, uint64_t* smem_lists, const ScanParams& p, int warp,
+                                                  int lane) {
+  __shared__ int is_last;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned t = atomicAdd(&p.tickets[blockIdx.y], 1u);
+    is_last = (t == gridDim.x - 1);
+    if (is_last) p.tickets[blockIdx.y] = 0;  // everybody else has already drawn: ready for the next launch
+  }
+  __syncthreads();
+  if (!is_last) return;
+  __threadfence();
+  tk.init(smem_lists + (size_t)warp * listbuf_len(p.kpad), p.k, p.kpad, lane);
+  const uint64_t* base = p.out + (size_t)blockIdx.y * gridDim.x * p.kpad;
+  const int total = (int)gridDim.x * p.kpad;
+  for (int i0 = warp * 32; i0 < total; i0 += kScanWarps * 32) {
+    const uint64_t key = (i0 + lane < total) ? __ldcg(base + i0 + lane) : 0ull;
+    tk.push(key > tk.thr, key, lane);
+  }
+  tk.flush(lane);
+  __syncthreads();
+  for (int s = 1; s < kScanWarps; s <<= 1) {
+    if ((warp & (2 * s - 1)) == 0 && warp + s < kScanWarps)
+      tk.merge_list(smem_lists + (size_t)(warp + s) * tk.len, lane);
+    __syncthreads();
+  }
+  if (warp == 0) {
+    const int64_t qi = blockIdx.y;
+    for (int i = lane; i < p.k; i += 32) {
+      const uint64_t key = tk.buf[i];
+      if (p.out_scores) p.out_scores[qi * p.k + i] = key ? key_score(key) : -INFINITY;
+      if (p.out_ids) p.out_ids[qi * p.k + i] = key ? (int64_t)key_id(key) : -1;
+    }
+    if (p.out_keys)
+      for (int i = lane; i < p.kpad; i += 32) p.out_keys[qi * p.kpad + i] = i < p.k ? tk.buf[i] : 0;
+  }
 }
 
 // G lanes per row, CPL 16-byte chunks per lane (row = G*CPL chunks), U row-slots in flight
@@ -130,6 +178,7 @@ __global__ void __launch_bounds__(kScanThreads, 2) scan_topk_kernel(const ScanPa
   }
   cta_reduce_and_store(tk, smem_lists, warp, lane,
                        p.out + ((size_t)blockIdx.y * gridDim.x + blockIdx.x) * p.kpad);
+  if (p.tickets) fused_final_merge(tk, smem_lists, p, warp, lane);
 }
 
 // any row length: one warp per row, chunks strided over the lanes, query in shared memory
@@ -193,6 +242,7 @@ __global__ void __launch_bounds__(kScanThreads, 2) scan_topk_generic_kernel(cons
   }
   cta_reduce_and_store(tk, smem_lists, warp, lane,
                        p.out + ((size_t)blockIdx.y * gridDim.x + blockIdx.x) * p.kpad);
+  if (p.tickets) fused_final_merge(tk, smem_lists, p, warp, lane);
 }
 
 }  // namespace ragb

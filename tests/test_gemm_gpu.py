@@ -39,6 +39,54 @@ def test_batched_vs_oracle(dtype, n, dim, nq, k):
         assert ref_search.recall_at_k(ids, rid) > 0.995
 
 
+@pytest.mark.parametrize("dtype,n,dim,nq,k", [
+    ("fp16", 60000, 384, 300, 100),   # BASELINE config 5's k: candidate buffers in global memory (kpad 128)
+    ("bf16", 50000, 384, 257, 100),
+    ("fp16", 30000, 768, 129, 50),    # kpad 64
+    ("fp16", 700, 128, 130, 128),     # k == kpad, fewer rows than fill the first prune
+    ("fp16", 90, 64, 200, 100),       # fewer rows than k: short lists
+])
+def test_batched_large_k_vs_oracle(dtype, n, dim, nq, k):
+    """k in (32, 128] runs on the SM-pair tensor-core kernel with per-query buffers of 2*kpad keys."""
+    FORCE_GEMM, _, _ = _flags()
+    rng = np.random.default_rng(n + dim + nq + k)
+    X = rng.standard_normal((n, dim)).astype(np.float32)
+    Q = rng.standard_normal((nq, dim)).astype(np.float32)
+    for i in range(0, nq, 9):
+        Q[i] = X[(i * 131) % n] + 0.3 * rng.standard_normal(dim).astype(np.float32)
+    s = _store(X, dtype)
+    import modular_rag_system_b200 as pkg
+    l0 = pkg.launch_count()
+    ids, sc = s.search(Q, k, "cosine")
+    assert pkg.launch_count() - l0 == 5, "expected convert + pair kernel + merge + chunk re-score + merge"
+    rid, _ = _check(ids, sc, X, Q, k, "cosine", -np.inf, False, TOL[dtype])
+    for i in range(0, nq, 9):
+        assert ids[i][0] == (i * 131) % n
+    if n < k:
+        assert (ids[:, n:] == -1).all() and (ids[:, :n] >= 0).all()
+    if dtype == "fp16":
+        assert ref_search.recall_at_k(ids, rid) > 0.995
+
+
+def test_batched_large_k_equals_scan_path():
+    FORCE_GEMM, FORCE_SCAN, _ = _flags()
+    rng = np.random.default_rng(13)
+    X = rng.standard_normal((40000, 384)).astype(np.float32)
+    X[100:140] = X[99]               # a run of exact ties straddling the candidate path
+    Q = rng.standard_normal((160, 384)).astype(np.float32)
+    Q[5] = X[99]
+    s = _store(X, "fp16")
+    valid = np.ones(40000, np.uint8); valid[::5] = 0
+    for kw in (dict(), dict(threshold=0.05, clamp01=True), dict(valid=valid), dict(row_begin=777, row_end=39000)):
+        a_ids, a_sc = s.search(Q, 100, "cosine", flags=FORCE_SCAN, **kw)
+        b_ids, b_sc = s.search(Q, 100, "cosine", **kw)
+        same = a_ids == b_ids
+        assert same.mean() > 0.99, kw
+        assert np.abs(a_sc[same] - b_sc[same])[np.isfinite(a_sc[same])].max() < 2e-6
+    ids, _ = s.search(Q, 100, "cosine")
+    assert ids[5][:41].tolist() == list(range(139, 98, -1))  # exact ties: newest (largest row) first
+
+
 def test_batched_equals_scan_path():
     FORCE_GEMM, FORCE_SCAN, NO_RESCORE = _flags()
     rng = np.random.default_rng(11)
