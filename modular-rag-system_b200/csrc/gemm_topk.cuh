@@ -344,77 +344,6 @@ __global__ void __launch_bounds__(256) rescore_kernel(const T* __restrict__ X, i
   if (lane == 0) keys[w] = sc >= threshold ? make_key(sc, id) : 0;
 }
 
-// ---- fp32 re-score of the selected CHUNKS (SM-pair kernel, gemm_pair.cuh) ----------------------
-// One warp per (query, selected chunk): lane == row of the chunk.  Each lane walks its own row in
-// 16-byte pieces against the fp32 query (uniform address: one broadcast load per piece), so the exact
-// fp32 score of row start+lane ends up in lane `lane` without any shuffle.  Applies what the scan
-// applies per row (:480-508): row range, valid mask, clamp, `>= threshold`.
-template <typename T>
-__global__ void __launch_bounds__(256) rescore_chunks_kernel(const T* __restrict__ X, int64_t ld, int dim,
-                                                             const float* __restrict__ q, int64_t nq, int metric,
-                                                             int flags, float threshold, int64_t row_begin,
-                                                             int64_t row_end, const uint8_t* __restrict__ valid,
-                                                             uint32_t id_base, int kpad,
-                                                             const uint64_t* __restrict__ chunk_keys /* [nq][kpad] */,
-                                                             uint64_t* __restrict__ out /* [nq][kpad*32] */) {
-  constexpr int E = Elem<T>::per16;
-  const int64_t w = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
-  const int lane = threadIdx.x & 31;
-  if (w >= nq * kpad) return;
-  const uint64_t key = chunk_keys[w];
-  uint64_t res = 0;
-  if (key != 0) {
-    const int64_t qi = w / kpad;
-    const float* qv = q + qi * dim;
-    float qq = 0.f;
-    if (metric == 1) {
-      for (int i = lane; i < dim; i += 32) { const float a = qv[i]; qq = fmaf(a, a, qq); }
-      qq = warp_sum(qq);
-    }
-    const float scale = metric == 1 ? (qq > 0.f ? rsqrtf(qq) : 0.f) : 1.f;
-    const int64_t row = (int64_t)key_id(key) + lane;
-    bool ok = row >= row_begin && row < row_end;
-    if (ok && valid) ok = valid[row] != 0;
-    if (ok) {
-      const uint4* rp = reinterpret_cast<const uint4*>(X + (size_t)row * ld);
-      const int pieces = dim / E, tail = dim - pieces * E;
-      float a0 = 0.f, a1 = 0.f;
-      int c = 0;
-      for (; c + 4 <= pieces; c += 4) {
-        uint4 v[4];
-#pragma unroll
-        for (int u = 0; u < 4; ++u) v[u] = rp[c + u];
-#pragma unroll
-        for (int u = 0; u < 4; ++u) {
-          float f[E];
-          Elem<T>::unpack(v[u], f);
-#pragma unroll
-          for (int i = 0; i < E; i += 2) {
-            a0 = fmaf(f[i], __ldg(qv + (c + u) * E + i), a0);
-            a1 = fmaf(f[i + 1], __ldg(qv + (c + u) * E + i + 1), a1);
-          }
-        }
-      }
-      for (; c < pieces; ++c) {
-        float f[E];
-        Elem<T>::unpack(rp[c], f);
-#pragma unroll
-        for (int i = 0; i < E; ++i) a0 = fmaf(f[i], __ldg(qv + c * E + i), a0);
-      }
-      if (tail) {  // dim % E != 0: the padding columns of the row are zero
-        float f[E];
-        Elem<T>::unpack(rp[pieces], f);
-#pragma unroll
-        for (int i = 0; i < E; ++i)
-          if (i < tail) a0 = fmaf(f[i], __ldg(qv + pieces * E + i), a0);
-      }
-      const float sc = finish_score(a0 + a1, scale, flags);
-      if (sc >= threshold) res = make_key(sc, (uint32_t)row + id_base);
-    }
-  }
-  out[w * 32 + lane] = res;
-}
-
 struct GemmState {
   CUtensorMap map_x;
   const void* map_rows = nullptr;  // allocation the map was built for

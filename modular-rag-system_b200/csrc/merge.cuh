@@ -57,4 +57,199 @@ __global__ void __launch_bounds__(kMergeThreads) merge_topk_kernel(const MergePa
   }
 }
 
+// ---------------------------------------------------------------------------------------------
+// K5' finish of the SM-pair batched kernel (gemm_pair.cuh), ONE launch, one CTA per query:
+//   1. fold the per-split lists of CHUNK keys (score = chunk maximum from the 16-bit-query tensor pass,
+//      id = local start row of the 32-row chunk) into the best k_sel chunks;
+//   2. score the 32 rows of each selected chunk exactly: fp32 query, fp32 accumulate, 8 lanes per row
+//      reading consecutive 16-byte pieces (a warp instruction touches 4 cache lines, not 32), and apply
+//      what the reference applies per row (ollama_rag_system.py:480-508): row window, valid mask, clamp,
+//      `>= threshold`;
+//   3. keep the k best rows (:511-515), decode to (score, global id).
+struct FinishParams {
+  const uint64_t* parts;  // [nq][n_lists][kpad] sorted chunk keys
+  int n_lists, kpad, k_sel, k;
+  const void* X;          // packed rows
+  int64_t ld;
+  int dim;
+  const float* q;         // [nq][dim] fp32
+  int metric, flags;
+  float threshold;
+  int64_t row_begin, row_end;
+  const uint8_t* valid;
+  uint32_t id_base;
+  float* out_scores;      // [nq][k] or null
+  int64_t* out_ids;       // [nq][k] or null
+  uint64_t* out_keys;     // [nq][kpad] or null
+};
+constexpr int kFinishChunkRows = 32;
+
+// number of keys of a descending-sorted list (zeros at the tail) that are greater than `key`
+__device__ __forceinline__ int count_greater_sorted(const uint64_t* list, int len_pow2, uint64_t key) {
+  int pos = 0;
+  for (int step = len_pow2 >> 1; step > 0; step >>= 1)
+    if (list[pos + step - 1] > key) pos += step;
+  return pos + (list[pos] > key ? 1 : 0);
+}
+
+// shared memory: lists [n_lists*kpad] | chunk [kpad] | cmax [kpad] | surv [kpad*32] | final [kpad] | misc
+__host__ __device__ inline size_t finish_smem_bytes(int n_lists, int kpad) {
+  return ((size_t)n_lists * kpad + (size_t)kpad * (3 + kFinishChunkRows)) * sizeof(uint64_t) + 16;
+}
+
+template <typename T>
+__global__ void __launch_bounds__(kMergeThreads, 3) finish_chunks_kernel(const FinishParams p) {
+  extern __shared__ __align__(16) uint64_t fsm[];
+  constexpr int E = Elem<T>::per16;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int64_t qi = blockIdx.x;
+  uint64_t* lists = fsm;
+  uint64_t* chunk = lists + (size_t)p.n_lists * p.kpad;  // selected chunk keys, by rank
+  uint64_t* cmax = chunk + p.kpad;                        // exact key of the best row of each selected chunk
+  uint64_t* surv = cmax + p.kpad;                         // rows that can still be among the k best
+  uint64_t* fin = surv + (size_t)p.kpad * kFinishChunkRows;
+  int* misc = reinterpret_cast<int*>(fin + p.kpad);       // [0] survivor count  [1..2] threshold key
+
+  // ---- 1. best k_sel chunks: rank every key by counting (lists are sorted, keys are unique) ----
+  const int n_keys = p.n_lists * p.kpad;
+  const uint64_t* base = p.parts + qi * (int64_t)n_keys;
+  for (int i = threadIdx.x; i < n_keys; i += kMergeThreads) lists[i] = base[i];
+  for (int i = threadIdx.x; i < p.kpad; i += kMergeThreads) { chunk[i] = 0; cmax[i] = 0; fin[i] = 0; }
+  if (threadIdx.x == 0) { misc[0] = 0; misc[1] = 0; misc[2] = 0; }
+  const float* qv = p.q + qi * p.dim;
+  float scale = 1.f;
+  if (p.metric == 1) {
+    float qq = 0.f;
+    for (int i = lane; i < p.dim; i += 32) { const float a = qv[i]; qq = fmaf(a, a, qq); }
+    qq = warp_sum(qq);
+    scale = qq > 0.f ? rsqrtf(qq) : 0.f;  // zero query scores 0.0 everywhere, :214-215
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < n_keys; i += kMergeThreads) {
+    const uint64_t key = lists[i];
+    if (key == 0) continue;
+    int rank = 0;
+    for (int l = 0; l < p.n_lists && rank < p.k_sel; ++l) rank += count_greater_sorted(lists + l * p.kpad, p.kpad, key);
+    if (rank < p.k_sel) chunk[rank] = key;
+  }
+  __syncthreads();
+
+  // ---- 2. exact scores of the rows of the selected chunks (registers: my_key of row start+lane) ----
+  const int g = lane >> 3, l = lane & 7;  // lane group g scores rows start + 4r + g, r = 0..7; 8 lanes per row
+  const int pieces = (int)(p.ld / E);     // ld is padded to 16 bytes, padding columns are zero
+  const bool q_vec = (p.dim % 4 == 0) && ((reinterpret_cast<uintptr_t>(qv) & 15) == 0);
+  for (int c = warp; c < p.k_sel; c += kMergeWarps) {
+    const uint64_t ckey = chunk[c];
+    if (ckey == 0) continue;  // warp-uniform
+    const int64_t start = (int64_t)key_id(ckey);
+    // per 16-byte piece of the query, eight independent row loads are in flight and the query piece is
+    // loaded once for all eight rows
+    float acc[8];
+#pragma unroll
+    for (int r = 0; r < 8; ++r) acc[r] = 0.f;
+    const T* x0 = static_cast<const T*>(p.X) + (size_t)(start + g) * p.ld;
+#pragma unroll 1
+    for (int pc = l; pc < pieces; pc += 8) {
+      float qf[E];
+      const int d0 = pc * E;
+      if (q_vec && d0 + E <= p.dim) {
+#pragma unroll
+        for (int i = 0; i < E; i += 4) {
+          const float4 t = __ldg(reinterpret_cast<const float4*>(qv + d0 + i));
+          qf[i] = t.x; qf[i + 1] = t.y; qf[i + 2] = t.z; qf[i + 3] = t.w;
+        }
+      } else {
+#pragma unroll
+        for (int i = 0; i < E; ++i) qf[i] = d0 + i < p.dim ? __ldg(qv + d0 + i) : 0.f;
+      }
+      uint4 v[8];
+#pragma unroll
+      for (int r = 0; r < 8; ++r)
+        v[r] = (start + 4 * r + g < p.row_end)
+                   ? ld_stream16(reinterpret_cast<const uint4*>(x0 + (size_t)(4 * r) * p.ld) + pc)
+                   : make_uint4(0, 0, 0, 0);
+#pragma unroll
+      for (int r = 0; r < 8; ++r) {
+        float f[E];
+        Elem<T>::unpack(v[r], f);
+        float a = acc[r];
+#pragma unroll
+        for (int i = 0; i < E; ++i) a = fmaf(f[i], qf[i], a);
+        acc[r] = a;
+      }
+    }
+    float mine = 0.f;
+#pragma unroll
+    for (int r = 0; r < 8; ++r) {
+      float a = acc[r];
+      a += __shfl_xor_sync(0xffffffffu, a, 4);
+      a += __shfl_xor_sync(0xffffffffu, a, 2);
+      a += __shfl_xor_sync(0xffffffffu, a, 1);
+      // lane L keeps the score of row start+L = start + 4*(L/4) + L%4: held by the 8 lanes of group L%4
+      const float v2 = __shfl_sync(0xffffffffu, a, (lane & 3) * 8);
+      if ((lane >> 2) == r) mine = v2;
+    }
+    const int64_t row = start + lane;
+    const float sc = finish_score(mine, scale, p.flags);
+    bool ok = row >= p.row_begin && row < p.row_end && sc >= p.threshold;
+    if (ok && p.valid) ok = p.valid[row] != 0;
+    const uint64_t key = ok ? make_key(sc, (uint32_t)row + p.id_base) : 0ull;
+    surv[c * kFinishChunkRows + lane] = key;  // parked; filtered below
+    uint64_t m = key;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const uint64_t t = __shfl_xor_sync(0xffffffffu, m, o);
+      m = t > m ? t : m;
+    }
+    if (lane == 0) cmax[c] = m;
+  }
+  __syncthreads();
+
+  // ---- 3. the k best rows (:511-515) ----
+  // the k-th best chunk-best key bounds the k-th best row from below: only rows at or above it are ranked
+  if (threadIdx.x < p.k_sel) {
+    const uint64_t key = cmax[threadIdx.x];
+    if (key != 0) {
+      int rank = 0;
+      for (int j = 0; j < p.k_sel; ++j) rank += cmax[j] > key ? 1 : 0;
+      if (rank == p.k - 1) { misc[1] = (int)(uint32_t)key; misc[2] = (int)(uint32_t)(key >> 32); }
+    }
+  }
+  __syncthreads();
+  const uint64_t tau = ((uint64_t)(uint32_t)misc[2] << 32) | (uint32_t)misc[1];  // 0 when fewer than k chunks hold a row
+  // compact the survivors in place: slot order does not matter, ranks are computed against the whole set
+  uint64_t mykeys[(128 * kFinishChunkRows) / kMergeThreads];
+  int n_mine = 0;
+  const int n_cand = p.k_sel * kFinishChunkRows;
+#pragma unroll
+  for (int u = 0; u < (128 * kFinishChunkRows) / kMergeThreads; ++u) {
+    const int i = threadIdx.x + u * kMergeThreads;
+    uint64_t key = 0;
+    if (i < n_cand && chunk[i / kFinishChunkRows] != 0) key = surv[i];
+    mykeys[u] = (key != 0 && key >= tau) ? key : 0ull;
+  }
+  __syncthreads();
+#pragma unroll
+  for (int u = 0; u < (128 * kFinishChunkRows) / kMergeThreads; ++u)
+    if (mykeys[u] != 0) { surv[atomicAdd(&misc[0], 1)] = mykeys[u]; ++n_mine; }
+  __syncthreads();
+  const int n_surv = misc[0];
+#pragma unroll
+  for (int u = 0; u < (128 * kFinishChunkRows) / kMergeThreads; ++u) {
+    const uint64_t key = mykeys[u];
+    if (key == 0) continue;
+    int rank = 0;
+    for (int j = 0; j < n_surv && rank < p.k; ++j) rank += surv[j] > key ? 1 : 0;
+    if (rank < p.k) fin[rank] = key;
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < p.k; i += kMergeThreads) {
+    const uint64_t key = fin[i];
+    if (p.out_scores) p.out_scores[qi * p.k + i] = key ? key_score(key) : -INFINITY;
+    if (p.out_ids) p.out_ids[qi * p.k + i] = key ? (int64_t)key_id(key) : -1;
+  }
+  if (p.out_keys)
+    for (int i = threadIdx.x; i < p.kpad; i += kMergeThreads) p.out_keys[qi * p.kpad + i] = i < p.k ? fin[i] : 0;
+}
+
 }  // namespace ragb

@@ -630,24 +630,29 @@ static int gemm_finish(ragb_store* s, const float* q, int64_t nq, int k, int kpa
   return merge_launch(tmp, nq, 1, kpad, kpad, kpad, k, out_scores, out_ids, out_keys, st, /*unsorted=*/true);
 }
 
-// SM-pair kernel epilogue: merge the per-split CHUNK lists, score the 32 rows of every selected chunk in fp32,
-// keep the k best rows
+// SM-pair kernel finish (merge.cuh: finish_chunks_kernel): fold the per-split CHUNK lists, score the 32 rows of every
+// selected chunk in fp32, keep the k best rows — one launch, one CTA per query
 static int gemm_finish_chunks(ragb_store* s, const float* q, int64_t nq, int k, int kpad, int k_sel, int metric,
                               float threshold, int flags, int64_t rb, int64_t re, const uint8_t* valid, uint32_t id_base,
-                              const uint64_t* parts, int splits, uint64_t* tmp, uint64_t* tmp_rows, uint64_t* out_keys,
-                              float* out_scores, int64_t* out_ids, cudaStream_t st) {
-  RB_TRY(merge_launch(parts, nq, splits, kpad, (int64_t)splits * kpad, kpad, k_sel, nullptr, nullptr, tmp, st));
-  const int64_t warps = nq * kpad;
-  const unsigned grid = (unsigned)((warps + 7) / 8);
-  if (s->dtype == RAGB_BF16)
-    rescore_chunks_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>((const __nv_bfloat16*)s->rows, s->ld, s->dim, q, nq, metric, flags,
-                                                              threshold, rb, re, valid, id_base, kpad, tmp, tmp_rows);
-  else
-    rescore_chunks_kernel<__half><<<grid, 256, 0, st>>>((const __half*)s->rows, s->ld, s->dim, q, nq, metric, flags, threshold,
-                                                       rb, re, valid, id_base, kpad, tmp, tmp_rows);
+                              const uint64_t* parts, int splits, uint64_t* out_keys, float* out_scores, int64_t* out_ids,
+                              cudaStream_t st) {
+  static_assert(kFinishChunkRows == kChunkRows, "epilogue and finish kernel disagree on the chunk size");
+  FinishParams f;
+  f.parts = parts; f.n_lists = splits; f.kpad = kpad; f.k_sel = k_sel; f.k = k;
+  f.X = s->rows; f.ld = s->ld; f.dim = s->dim; f.q = q; f.metric = metric; f.flags = flags; f.threshold = threshold;
+  f.row_begin = rb; f.row_end = re; f.valid = valid; f.id_base = id_base;
+  f.out_scores = out_scores; f.out_ids = out_ids; f.out_keys = out_keys;
+  const size_t smem = finish_smem_bytes(splits, kpad);
+  if (smem > 200 * 1024) return fail(RAGB_EUNSUPPORTED, "internal: %d splits x kpad %d do not fit the finish kernel", splits, kpad);
+  if (s->dtype == RAGB_BF16) {
+    if (smem > 48 * 1024) CU_TRY(cudaFuncSetAttribute(finish_chunks_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    finish_chunks_kernel<__nv_bfloat16><<<(unsigned)nq, kMergeThreads, smem, st>>>(f);
+  } else {
+    if (smem > 48 * 1024) CU_TRY(cudaFuncSetAttribute(finish_chunks_kernel<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    finish_chunks_kernel<__half><<<(unsigned)nq, kMergeThreads, smem, st>>>(f);
+  }
   LAUNCHED();
-  return merge_launch(tmp_rows, nq, kChunkRows, kpad, (int64_t)kChunkRows * kpad, kpad, k, out_scores, out_ids, out_keys, st,
-                      /*unsorted=*/true);
+  return RAGB_OK;
 }
 
 // SM-pair kernel (gemm_pair.cuh): tcgen05.mma.cta_group::2, M=256 (two query tiles) x N=256
@@ -715,22 +720,18 @@ static int gemm_pair_search(ragb_store* s, const float* q, int64_t nq, int k, in
   p.id_base = 0;  // chunk keys carry LOCAL start rows; the re-score adds id_base
   p.idesc = umma_idesc(s->dtype == RAGB_BF16, 2 * kGemmM, kPairN);
   const size_t part_bytes = (size_t)nq_pad * splits * kpad * sizeof(uint64_t);
-  const size_t tmp_bytes = (size_t)nq * kpad * sizeof(uint64_t);
-  const size_t rows_bytes = tmp_bytes * kChunkRows;
   const size_t cand_bytes = E == 2 ? 0 : (size_t)n_qt * splits * kGemmM * (32 * E) * sizeof(uint64_t);
-  RB_TRY(grow(&s->ws, &s->ws_bytes, part_bytes + tmp_bytes + rows_bytes + cand_bytes, false));
+  RB_TRY(grow(&s->ws, &s->ws_bytes, part_bytes + cand_bytes, false));
   p.out = (uint64_t*)s->ws;
-  uint64_t* tmp = (uint64_t*)((char*)s->ws + part_bytes);
-  uint64_t* tmp_rows = (uint64_t*)((char*)s->ws + part_bytes + tmp_bytes);
-  p.cand_ws = E == 2 ? nullptr : (uint64_t*)((char*)s->ws + part_bytes + tmp_bytes + rows_bytes);
+  p.cand_ws = E == 2 ? nullptr : (uint64_t*)((char*)s->ws + part_bytes);
   cfg.gridDim = dim3((unsigned)(n_qt * splits));
   {
     ProfScope prof(s, st);
     CU_TRY(cudaLaunchKernelEx(&cfg, kern, map_q, g->map_x_pair, p));
   }
   LAUNCHED();
-  return gemm_finish_chunks(s, q, nq, k, kpad, k_sel, metric, threshold, flags, rb, re, valid, id_base, p.out, splits, tmp,
-                            tmp_rows, out_keys, out_scores, out_ids, st);
+  return gemm_finish_chunks(s, q, nq, k, kpad, k_sel, metric, threshold, flags, rb, re, valid, id_base, p.out, splits,
+                            out_keys, out_scores, out_ids, st);
 }
 
 // query-stationary tcgen05 kernel (gemm_ts.cuh); returns RAGB_EUNSUPPORTED when the shape does not fit
