@@ -208,11 +208,13 @@ def fill_store(pkg, torch, wl, r0, r1, device):
     return store
 
 
-def time_device(torch, dist, fn, steps, warmup, world):
+def time_device(torch, dist, fn, steps, warmup, world, after_warmup=None):
     """W warm-ups, then K steps between barrier+sync, CUDA events on the launching stream; max over ranks (ms)."""
     for _ in range(warmup):
         fn()
     torch.cuda.synchronize()
+    if after_warmup is not None:
+        after_warmup()
     if world > 1:
         dist.barrier()
         torch.cuda.synchronize()
@@ -251,12 +253,10 @@ def time_host(torch, dist, fn, steps, warmup, world):
     return ms
 
 
-def roofline_obj(kind, store, torch, fn, iters, work_per_launch, pk, pk_src, sustained):
-    """Kernel-only time of the dominant kernel from the C ABI's event brackets -> roofline object."""
-    store.profile(True)
-    for _ in range(iters):
-        fn()
-    torch.cuda.synchronize()
+def roofline_obj(kind, store, work_per_launch, pk, pk_src, sustained):
+    """Kernel-only time of the dominant kernel -> roofline object.  The C ABI brackets that kernel with CUDA
+    events on the launching stream (ragb_store_profile); they were armed for the timed steps themselves, so the
+    kernel time and the step time come from the same launches."""
     ms, n = store.profile_read()
     store.profile(False)
     per = ms / max(n, 1)
@@ -270,6 +270,17 @@ def roofline_obj(kind, store, torch, fn, iters, work_per_launch, pk, pk_src, sus
     return {"bound": kind, "achieved": achieved, "peak": peak, "unit": unit, "frac": achieved / peak,
             "traffic": None, "kernel_ms": per, "launches_timed": n, "peak_source": pk_src +
             (", sustained" if (kind == "tensor" and sustained) else ", burst" if kind == "tensor" else "")}
+
+
+def attach_traffic(roof, key):
+    """roofline.traffic = dram bytes read+written per launch of that kernel from the committed `ncu --set full` capture."""
+    try:
+        tr = json.loads((ROOT / "profiles" / "traffic.json").read_text()).get(key)
+        if tr:
+            roof["traffic"] = tr["bytes"]
+            roof["traffic_source"] = tr["source"]
+    except Exception:
+        pass
 
 
 def run_b200(args):
@@ -308,10 +319,14 @@ def run_b200(args):
     step = (lambda: searcher.search_dev(Q, k, "ip"))
     l0 = pkg.launch_count()
     with ClockSampler(local) as cs:
-        ms = time_device(torch, dist, step, args.steps, args.warmup, world)
+        ms = time_device(torch, dist, step, args.steps, args.warmup, world, after_warmup=lambda: store.profile(True))
     launches = (pkg.launch_count() - l0) * args.steps // (args.steps + args.warmup)
     clocks = cs.summary()
     qps = B * args.steps / (ms / 1e3)
+    # roofline of the dominant kernel (this rank's shard): its event brackets were armed for exactly these steps
+    tensor_path = B >= 4
+    work = 2.0 * B * (r1 - r0) * d if tensor_path else float(r1 - r0) * d * 2
+    roof = roofline_obj("tensor" if tensor_path else "hbm", store, work, pk, pk_src, sustained=(ms / args.steps > 50.0))
 
     # ---- end-to-end leg (host buffers through the public entry point) ---------------
     if world == 1:
@@ -323,20 +338,9 @@ def run_b200(args):
            "d2h_bytes_per_step": B * k * 12, "ms_per_step": ms_e2e / args.steps,
            "entry": "ragb_search (C ABI, host pointers)" if world == 1 else "ShardedSearcher.search (host arrays)"}
 
-    # ---- roofline of the dominant kernel (this rank's shard), measured live ---------
-    tensor_path = B >= 4
-    work = 2.0 * B * (r1 - r0) * d if tensor_path else float(r1 - r0) * d * 2
-    roof = roofline_obj("tensor" if tensor_path else "hbm", store, torch, step, max(3, min(args.steps, 10)), work,
-                        pk, pk_src, sustained=(ms / args.steps > 50.0))
     roof["kernel"] = ("gemm_topk_pair_kernel (tcgen05.mma cta_group::2 + TMA, fused top-k)" if tensor_path
                       else "scan_topk_kernel")
-    try:
-        tr = json.loads((ROOT / "profiles" / "traffic.json").read_text()).get(f"{args.workload}_b{B}_n{world}")
-        if tr:
-            roof["traffic"] = tr["bytes"]
-            roof["traffic_source"] = tr["source"]
-    except Exception:
-        pass
+    attach_traffic(roof, f"{args.workload}_b{B}_n{world}")
     roof["kernel_share_of_step"] = roof["kernel_ms"] / (ms / args.steps)
 
     extras = []
@@ -380,10 +384,12 @@ def run_extras(args, pkg, torch, store, wl, pk, pk_src):
         Q = (Q / Q.norm(dim=1, keepdim=True)).contiguous()
         fn = (lambda: st.search_dev(Q, args.k, "ip"))
         steps = 50 if B == 1 else args.steps
-        ms = time_device(torch, None, fn, steps, args.warmup, 1)
+        ms = time_device(torch, None, fn, steps, args.warmup, 1, after_warmup=lambda: st.profile(True))
         tensor = B >= 4
         work = 2.0 * B * len(st) * w["d"] if tensor else float(len(st)) * w["d"] * 2
-        roof = roofline_obj("tensor" if tensor else "hbm", st, torch, fn, 10, work, pk, pk_src, sustained=False)
+        roof = roofline_obj("tensor" if tensor else "hbm", st, work, pk, pk_src, sustained=False)
+        roof["kernel_share_of_step"] = roof["kernel_ms"] / (ms / steps)
+        attach_traffic(roof, f"{name}_b{B}_n1")
         out.append({"workload": f"{name} batch {B}", "value": B * steps / (ms / 1e3), "unit": "queries/s",
                     "ms_per_step": ms / steps, "roofline": roof})
 

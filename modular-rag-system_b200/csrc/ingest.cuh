@@ -113,31 +113,54 @@ __device__ __forceinline__ float block_sum(float v, float* red) {
 
 constexpr int kPoolThreads = 256;
 
-// dynamic shared memory: float w[seq] | float acc[groups][W][8] | float v[chunks*8] | float red[8]
+// dynamic shared memory: float wt[seq] | int idx[seq] | float acc[groups][W][8] | float v[chunks*8] | float red[8] | int cnt[9]
 template <typename Tin, typename Tm, typename Tout>
-__global__ void __launch_bounds__(kPoolThreads) pool_norm_pack_kernel(
+__global__ void __launch_bounds__(kPoolThreads, 3) pool_norm_pack_kernel(
     const Tin* __restrict__ tok, const Tm* __restrict__ mask, int seq, int hidden,
     Tout* __restrict__ out, int64_t ld_out, float* __restrict__ norms, bool vec_ok) {
   extern __shared__ __align__(16) float sm[];
-  // token rows in flight per thread: 16-bit inputs move 16 B per row, so they need twice as many
-  constexpr int kPoolUnroll = sizeof(Tin) == 2 ? 16 : 8;
+  // token rows in flight per thread
+  constexpr int kPoolUnroll = sizeof(Tin) == 2 ? 12 : 8;
   const int chunks = (hidden + 7) / 8;
   const int W = chunks < kPoolThreads ? chunks : kPoolThreads;
   const int groups = kPoolThreads / W;
-  float* w = sm;
-  float* accs = w + ((seq + 3) & ~3);
+  const int seq4 = (seq + 3) & ~3;
+  float* wt = sm;                                     // weights of the tokens that count, compacted
+  int* idx = reinterpret_cast<int*>(wt + seq4);       // their positions
+  float* accs = reinterpret_cast<float*>(idx + seq4);
   float* v = accs + (size_t)groups * W * 8;
   float* red = v + (size_t)chunks * 8;
+  int* wcnt = reinterpret_cast<int*>(red + 8);        // per-warp counts of one compaction round, [8] = running total
   const int64_t b = blockIdx.x;
-  const int t = threadIdx.x;
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
 
+  // ---- mask: total weight, and the list of tokens with a non-zero weight (the others are never fetched) ----
   float wsum = 0.f;
-  for (int s = t; s < seq; s += kPoolThreads) {
-    float m = mask ? mask_weight(mask[b * seq + s]) : 1.0f;
-    w[s] = m;
+  if (t == 0) wcnt[8] = 0;
+  for (int s0 = 0; s0 < seq; s0 += kPoolThreads) {
+    const int s = s0 + t;
+    const float m = s < seq ? (mask ? mask_weight(mask[b * seq + s]) : 1.0f) : 0.f;
     wsum += m;
+    const unsigned bal = __ballot_sync(0xffffffffu, m != 0.f);
+    if (lane == 0) wcnt[warp] = __popc(bal);
+    __syncthreads();
+    int off = wcnt[8];
+    for (int w2 = 0; w2 < warp; ++w2) off += wcnt[w2];
+    if (m != 0.f) {
+      const int pos = off + __popc(bal & ((1u << lane) - 1u));
+      wt[pos] = m;
+      idx[pos] = s;
+    }
+    __syncthreads();
+    if (t == 0) {
+      int tot = wcnt[8];
+      for (int w2 = 0; w2 < kPoolThreads / 32; ++w2) tot += wcnt[w2];
+      wcnt[8] = tot;
+    }
+    __syncthreads();
   }
-  wsum = block_sum(wsum, red);  // includes the barrier that publishes w[]
+  wsum = block_sum(wsum, red);  // includes the barriers that publish wt[], idx[] and the count
+  const int nv = wcnt[8];
   const float inv_cnt = 1.0f / fmaxf(wsum, 1e-9f);
 
   const int g = t / W, col = t - g * W;
@@ -151,19 +174,21 @@ __global__ void __launch_bounds__(kPoolThreads) pool_norm_pack_kernel(
     if (active && c < chunks) {
       constexpr int NV = sizeof(Tin) == 2 ? 1 : 2;  // 16-byte loads per 8 elements
       const bool fast = vec_ok && (c * 8 + 8 <= hidden);
-      for (int s0 = g; s0 < seq; s0 += groups * kPoolUnroll) {
+      const Tin* colbase = base + c * 8;
+      for (int j0 = g; j0 < nv; j0 += groups * kPoolUnroll) {
         float ws[kPoolUnroll];
         if (fast) {
           // phase 1: every load of the batch is in flight before anything waits on one
           uint4 raw[kPoolUnroll][NV];
 #pragma unroll
           for (int u = 0; u < kPoolUnroll; ++u) {
-            const int s = s0 + u * groups;
-            ws[u] = s < seq ? w[s] : 0.f;
-            const Tin* src = base + (size_t)s * hidden + c * 8;
+            const int j = j0 + u * groups;
+            const bool in = j < nv;
+            ws[u] = in ? wt[j] : 0.f;
+            const Tin* src = colbase + (size_t)(in ? idx[j] : 0) * hidden;
 #pragma unroll
-            for (int v = 0; v < NV; ++v)
-              raw[u][v] = ws[u] != 0.f ? ld_stream16(reinterpret_cast<const char*>(src) + 16 * v) : make_uint4(0, 0, 0, 0);
+            for (int q = 0; q < NV; ++q)
+              raw[u][q] = in ? ld_stream16(reinterpret_cast<const char*>(src) + 16 * q) : make_uint4(0, 0, 0, 0);
           }
           // phase 2: convert and accumulate
 #pragma unroll
@@ -177,13 +202,13 @@ __global__ void __launch_bounds__(kPoolThreads) pool_norm_pack_kernel(
         } else {
 #pragma unroll
           for (int u = 0; u < kPoolUnroll; ++u) {
-            const int s = s0 + u * groups;
-            ws[u] = s < seq ? w[s] : 0.f;
-            if (ws[u] != 0.f) {
+            const int j = j0 + u * groups;
+            if (j < nv) {
               float f[8];
-              load8_stream(base + (size_t)s * hidden, c, hidden, false, f);
+              load8_stream(base + (size_t)idx[j] * hidden, c, hidden, false, f);
+              const float wj = wt[j];
 #pragma unroll
-              for (int e = 0; e < 8; ++e) acc[e] = fmaf(ws[u], f[e], acc[e]);
+              for (int e = 0; e < 8; ++e) acc[e] = fmaf(wj, f[e], acc[e]);
             }
           }
         }

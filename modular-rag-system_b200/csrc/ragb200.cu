@@ -286,7 +286,7 @@ static int pool_launch(const void* tok, const void* mask, int64_t batch, int seq
   const int chunks = (hidden + 7) / 8;
   const int W = chunks < kPoolThreads ? chunks : kPoolThreads;
   const int groups = kPoolThreads / W;
-  const size_t smem = sizeof(float) * (((size_t)seq + 3) / 4 * 4 + (size_t)groups * W * 8 + (size_t)chunks * 8 + 8);
+  const size_t smem = sizeof(float) * (2 * (((size_t)seq + 3) / 4 * 4) + (size_t)groups * W * 8 + (size_t)chunks * 8 + 8 + 12);
   auto kern = pool_norm_pack_kernel<Tin, Tm, Tout>;
   if (smem > 48 * 1024) {
     if (smem > 200 * 1024) return fail(RAGB_EUNSUPPORTED, "seq %d x hidden %d needs %zu B of shared memory", seq, hidden, smem);
