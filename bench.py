@@ -36,8 +36,11 @@ WORKLOADS = {
     "10Mx768": dict(n=10_000_000, d=768, dtype="fp16"),
     # BASELINE.json configs[1]
     "1Mx384": dict(n=1_000_000, d=384, dtype="fp16"),
+    # BASELINE.json configs[4]: run with --k 100 --batch 4096 (--gpus 8: 9.6 GB per GPU; one GPU holds all 76.8 GB too)
+    "100Mx384": dict(n=100_000_000, d=384, dtype="bf16"),
 }
-METRIC = "queries/sec exact top-10"
+def metric_name(k):
+    return f"queries/sec exact top-{k}"
 FALLBACK_PEAKS = {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0}
 
 
@@ -50,6 +53,8 @@ def parse_args():
     ap.add_argument("--workload", default="10Mx768", choices=sorted(WORKLOADS))
     ap.add_argument("--batch", type=int, default=1024)
     ap.add_argument("--k", type=int, default=10)
+    ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"],
+                    help="N > 1: candidates stored into peer memory by the search kernels (default) or NCCL all-gather")
     ap.add_argument("--no-extras", action="store_true", help="skip the secondary cases (batch 1, 1Mx384)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline leg")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target CPU time of one baseline sample")
@@ -126,7 +131,7 @@ def run_reference(args):
     qps = sum(vals) / len(vals)
     obj["value"] = qps
     line = {
-        "impl": "reference", "metric": METRIC, "value": qps, "unit": "queries/s", "n_gpus": args.gpus,
+        "impl": "reference", "metric": metric_name(args.k), "value": qps, "unit": "queries/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": 1e3 * args.batch / qps, "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
@@ -306,12 +311,12 @@ def run_b200(args):
     bounds = pkg.shard_bounds(n, world)
     r0, r1 = bounds[rank]
     store = fill_store(pkg, torch, wl, r0, r1, local)
-    searcher = pkg.ShardedSearcher(store, r0)
+    searcher = pkg.ShardedSearcher(store, r0, exchange=args.exchange)
     gq = torch.Generator(device="cuda").manual_seed(1)
     Q = torch.randn((B, d), generator=gq, device="cuda")
     Q = (Q / Q.norm(dim=1, keepdim=True)).contiguous()
     Qh = Q.cpu().numpy()
-    if world > 1:  # warm NCCL up outside every timed region
+    if world > 1:  # set the exchange up (symmetric memory rendezvous / NCCL communicator) outside every timed region
         searcher.search_dev(Q, k)
         torch.cuda.synchronize()
 
@@ -355,14 +360,19 @@ def run_b200(args):
         t = torch.tensor([launches], device="cuda", dtype=torch.int64)
         dist.all_reduce(t)
         launches = int(t.item())
+    if world > 1:
+        searcher.check()  # a merge that timed out waiting for a rank invalidates the run
     if rank == 0:
         line = {
-            "metric": METRIC, "value": qps, "unit": "queries/s", "n_gpus": world, "steps": args.steps,
+            "metric": metric_name(k), "value": qps, "unit": "queries/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong",
-            "vs_baseline": None, "dtype": "f16 operands, f32 accumulate", "data": "synthetic",
-            "config": {"workload": f"{args.workload} fp16 unit rows, inner product, exact top-{k}, batch {B}",
+            "vs_baseline": None, "dtype": f"{wl['dtype']} operands, f32 accumulate", "data": "synthetic",
+            "config": {"workload": f"{args.workload} {wl['dtype']} unit rows, inner product, exact top-{k}, batch {B}",
                        "rows_total": n, "dim": d, "batch": B, "k": k,
-                       "parallelism": f"rows sharded over {world} GPU(s), all-gather of k candidates + merge",
+                       "parallelism": (f"rows sharded over {world} GPUs; each rank's finish kernel stores its k candidates per "
+                                       f"query into every rank's gather buffer over NVLink (peer memory), merge kernel waits "
+                                       f"on the arrival words" if world > 1 and args.exchange == "peer" else
+                                       f"rows sharded over {world} GPU(s), NCCL all-gather of k candidates + merge"),
                        "l2": f"corpus shard {(r1 - r0) * d * 2 / 1e6:.0f} MB per GPU vs 126 MB L2: no flush needed"
                              if (r1 - r0) * d * 2 > 4 * 126e6 else "corpus shard comparable to L2; not flushed"},
             "e2e": e2e, "roofline": roof, "cpu_baseline": cpu, "gpu_launches": launches, "clocks": clocks,

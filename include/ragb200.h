@@ -146,6 +146,30 @@ int ragb_merge_keys_dev(int device, const uint64_t* keys, int64_t nq, int n_list
                         int64_t stride_q, int64_t stride_p, int k, float* out_scores,
                         int64_t* out_ids, void* stream);
 
+
+/* ---- candidate exchange over peer memory (NVLink P2P), no collective launch ----------------------
+ * Every rank owns a gather buffer uint64 keys[world][nq][kpad] and `world` uint64 arrival words, both
+ * mapped into every other rank's address space (CUDA IPC / torch symmetric memory).
+ * ragb_search_scatter_dev = ragb_search_keys_dev whose LAST kernel stores this rank's sorted keys
+ * straight into slot [rank] of every rank's buffer and then publishes `epoch` to word [rank] of every
+ * rank (release, system scope).  ragb_gather_merge_dev waits (acquire, system scope; ~2 s timeout ->
+ * *out_status = 1) until all `world` words of this rank have reached `epoch`, then merges its buffer.
+ * Alternate between two buffers from call to call (keys[] of epoch e+1 must not alias those of e);
+ * epochs are strictly increasing.  The reference is single-device: there is nothing this replaces. */
+#define RAGB_MAX_PEERS 8
+typedef struct ragb_exchange {
+  int world, rank;
+  uint64_t* keys[RAGB_MAX_PEERS];  /* keys[r]  = rank r's gather buffer of this epoch */
+  uint64_t* flags[RAGB_MAX_PEERS]; /* flags[r] = rank r's arrival words [world] */
+  uint64_t epoch;
+} ragb_exchange;
+int ragb_search_scatter_dev(ragb_store* s, const float* q, int64_t nq, int k, int metric,
+                            float threshold, int flags, int64_t row_begin, int64_t row_end,
+                            const uint8_t* valid, uint32_t id_base, const ragb_exchange* x,
+                            void* stream);
+int ragb_gather_merge_dev(int device, const ragb_exchange* x, int64_t nq, int k, float* out_scores,
+                          int64_t* out_ids, int* out_status, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

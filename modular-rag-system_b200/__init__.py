@@ -5,9 +5,9 @@
 ``ShardedSearcher``  row-sharded multi-GPU search, one process per GPU (torch.distributed / NCCL)
 """
 from ._lib import RagbError, build, lib  # noqa: F401
-from .store import DeviceStore, kpad_of, launch_count, merge_keys_dev  # noqa: F401
-from .sharded import ShardedSearcher, shard_bounds  # noqa: F401
+from .store import DeviceStore, gather_merge_dev, kpad_of, launch_count, merge_keys_dev  # noqa: F401
+from .sharded import PeerBuffers, ShardedSearcher, shard_bounds  # noqa: F401
 from .rag_store import B200VectorStore, RAGDocument, RAGQuery, RAGResult, install  # noqa: F401
 
 __all__ = ["DeviceStore", "RagbError", "build", "lib", "kpad_of", "launch_count", "merge_keys_dev",
-           "ShardedSearcher", "shard_bounds", "B200VectorStore", "RAGDocument", "RAGQuery", "RAGResult", "install"]
+           "ShardedSearcher", "PeerBuffers", "gather_merge_dev", "shard_bounds", "B200VectorStore", "RAGDocument", "RAGQuery", "RAGResult", "install"]

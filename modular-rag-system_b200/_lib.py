@@ -22,6 +22,15 @@ OK, EINVAL, ECUDA, ENOMEM, EFULL, EUNSUPPORTED = 0, -1, -2, -3, -4, -5
 _vp, _i, _i64, _f = C.c_void_p, C.c_int, C.c_int64, C.c_float
 _pi64 = C.POINTER(C.c_int64)
 
+MAX_PEERS = 8
+
+
+class Exchange(C.Structure):
+    """struct ragb_exchange (include/ragb200.h): peer-mapped gather buffers and arrival words of one epoch."""
+    _fields_ = [("world", C.c_int), ("rank", C.c_int), ("keys", C.c_void_p * MAX_PEERS),
+                ("flags", C.c_void_p * MAX_PEERS), ("epoch", C.c_uint64)]
+
+
 # name -> (restype, argtypes); every symbol include/ragb200.h declares
 SIGNATURES = {
     "ragb_abi_version": (_i, []),
@@ -55,6 +64,8 @@ SIGNATURES = {
     "ragb_kpad": (_i, [_i]),
     "ragb_search_keys_dev": (_i, [_vp, _vp, _i64, _i, _i, _f, _i, _i64, _i64, _vp, C.c_uint32, _vp, _vp]),
     "ragb_merge_keys_dev": (_i, [_i, _vp, _i64, _i, _i, _i64, _i64, _i, _vp, _vp, _vp]),
+    "ragb_search_scatter_dev": (_i, [_vp, _vp, _i64, _i, _i, _f, _i, _i64, _i64, _vp, C.c_uint32, C.POINTER(Exchange), _vp]),
+    "ragb_gather_merge_dev": (_i, [_i, C.POINTER(Exchange), _i64, _i, _vp, _vp, _vp, _vp]),
 }
 
 

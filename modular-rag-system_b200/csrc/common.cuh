@@ -38,6 +38,50 @@ __device__ __forceinline__ uint64_t make_key(float s, uint32_t id) {
 __device__ __forceinline__ float key_score(uint64_t k) { return unorder_bits((uint32_t)(k >> 32)); }
 __device__ __forceinline__ uint32_t key_id(uint64_t k) { return (uint32_t)k; }
 
+// ---------------------------------------------------------------------------
+// Candidate exchange over peer memory (row-sharded corpus, one process per GPU).
+// The kernel that produces a rank's final keys stores them straight into EVERY rank's gather buffer
+// (its own included) through peer-mapped pointers — NVLink P2P stores, no collective launch — and the
+// last CTA to finish publishes an epoch word to every rank with release semantics at system scope.
+// The merge kernel of each rank waits on its `world` epoch words (acquire, system scope) and folds.
+// ---------------------------------------------------------------------------
+constexpr int kMaxPeers = 8;
+struct PeerOut {
+  uint64_t* keys[kMaxPeers];        // rank p's gather buffer, already offset to THIS rank's [nq][kpad] slot
+  uint64_t* flag[kMaxPeers];        // rank p's arrival word of THIS rank
+  unsigned* done;                   // CTA completion counter of this launch (zero between launches)
+  unsigned long long epoch;
+  int n;                            // ranks (0 = exchange off)
+};
+__device__ __forceinline__ void peer_emit(const PeerOut& po, int64_t idx, uint64_t key) {
+  for (int r = 0; r < po.n; ++r) po.keys[r][idx] = key;
+}
+// every thread of the CTA calls it after its peer_emit()s; n_ctas = CTAs that will call it in this launch
+__device__ __forceinline__ void peer_signal(const PeerOut& po, unsigned n_ctas) {
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned t = atomicAdd(po.done, 1u);
+    if (t == n_ctas - 1) {
+      *po.done = 0;  // everybody else has already arrived: ready for the next launch
+      __threadfence_system();
+      for (int r = 0; r < po.n; ++r)
+        asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(po.flag[r]), "l"(po.epoch) : "memory");
+    }
+  }
+}
+// thread r < n waits until rank r's epoch word has reached `epoch`; returns false on timeout (~2 s)
+__device__ __forceinline__ bool peer_wait(const uint64_t* flag, unsigned long long epoch) {
+  const long long t0 = clock64();
+  for (;;) {
+    unsigned long long v;
+    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(flag) : "memory");
+    if (v >= epoch) return true;
+    if (clock64() - t0 > 4000000000ll) return false;
+    __nanosleep(200);
+  }
+}
+
 // score post-processing shared by every search kernel
 __device__ __forceinline__ float finish_score(float dot, float scale, int flags) {
   float s = dot * scale;

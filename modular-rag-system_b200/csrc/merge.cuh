@@ -19,12 +19,21 @@ struct MergeParams {
   float* out_scores;    // [nq][k] or null
   int64_t* out_ids;     // [nq][k] or null
   uint64_t* out_keys;   // [nq][kpad] or null (sorted keys, for a later merge level)
+  PeerOut peers;        // peers.n > 0: the kpad sorted keys also go to every rank's gather buffer
+  const uint64_t* wait_flags;  // wait_n > 0: first wait until wait_flags[0..wait_n) have reached wait_epoch
+  int wait_n;
+  unsigned long long wait_epoch;
+  int* status;          // set to 1 when the wait timed out (a rank never arrived)
 };
 
 __global__ void __launch_bounds__(kMergeThreads) merge_topk_kernel(const MergeParams p) {
   extern __shared__ __align__(16) uint64_t smem_lists[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int64_t qi = blockIdx.x;
+  if (p.wait_n > 0) {  // candidate lists arrive from the other GPUs through peer stores
+    if ((int)threadIdx.x < p.wait_n && !peer_wait(p.wait_flags + threadIdx.x, p.wait_epoch) && p.status) atomicExch(p.status, 1);
+    __syncthreads();
+  }
   WarpTopK tk;
   tk.init(smem_lists + (size_t)warp * listbuf_len(p.kpad), p.k, p.kpad, lane);
   const uint64_t* base = p.keys + qi * p.stride_q;
@@ -54,7 +63,10 @@ __global__ void __launch_bounds__(kMergeThreads) merge_topk_kernel(const MergePa
     }
     if (p.out_keys)
       for (int i = lane; i < p.kpad; i += 32) p.out_keys[qi * p.kpad + i] = i < p.k ? tk.buf[i] : 0;
+    if (p.peers.n)
+      for (int i = lane; i < p.kpad; i += 32) peer_emit(p.peers, qi * p.kpad + i, i < p.k ? tk.buf[i] : 0);
   }
+  if (p.peers.n) peer_signal(p.peers, gridDim.x);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -81,6 +93,7 @@ struct FinishParams {
   float* out_scores;      // [nq][k] or null
   int64_t* out_ids;       // [nq][k] or null
   uint64_t* out_keys;     // [nq][kpad] or null
+  PeerOut peers;          // peers.n > 0: the kpad sorted keys also go to every rank's gather buffer
 };
 constexpr int kFinishChunkRows = 32;
 
@@ -250,6 +263,10 @@ __global__ void __launch_bounds__(kMergeThreads, 3) finish_chunks_kernel(const F
   }
   if (p.out_keys)
     for (int i = threadIdx.x; i < p.kpad; i += kMergeThreads) p.out_keys[qi * p.kpad + i] = i < p.k ? fin[i] : 0;
+  if (p.peers.n) {
+    for (int i = threadIdx.x; i < p.kpad; i += kMergeThreads) peer_emit(p.peers, qi * p.kpad + i, i < p.k ? fin[i] : 0);
+    peer_signal(p.peers, gridDim.x);
+  }
 }
 
 }  // namespace ragb

@@ -74,7 +74,9 @@ struct ragb_store {
   // search workspace (guarded by search_mu)
   void* ws = nullptr;
   size_t ws_bytes = 0;
-  unsigned* tickets = nullptr;  // [kScanMaxQ] zero between launches: last-CTA final merge of the scan (scan.cuh)
+  unsigned* tickets = nullptr;  // [kScanMaxQ + 1] zero between launches: last-CTA final merge of the scan (scan.cuh);
+                                // the extra word counts finished CTAs for the peer exchange signal
+  PeerOut peer = {};            // set for the duration of ragb_search_scatter_dev (guarded by search_mu)
   // ingest staging (guarded by add_mu)
   void* stage_dev = nullptr;
   size_t stage_dev_bytes = 0;
@@ -174,9 +176,9 @@ extern "C" int ragb_store_create(int device, int dim, int dtype, int64_t capacit
   if (r != RAGB_OK) { delete s; return r; }
   e = cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking);
   if (e != cudaSuccess) { cudaFree(s->rows); cudaFree(s->norms); delete s; return fail(RAGB_ECUDA, "cudaStreamCreate: %s", cudaGetErrorString(e)); }
-  e = cudaMalloc(&s->tickets, kScanMaxQ * sizeof(unsigned));
+  e = cudaMalloc(&s->tickets, (kScanMaxQ + 1) * sizeof(unsigned));
   if (e != cudaSuccess) { cudaStreamDestroy(s->stream); cudaFree(s->rows); cudaFree(s->norms); delete s; return fail(RAGB_ENOMEM, "cudaMalloc tickets: %s", cudaGetErrorString(e)); }
-  cudaMemsetAsync(s->tickets, 0, kScanMaxQ * sizeof(unsigned), s->stream);
+  cudaMemsetAsync(s->tickets, 0, (kScanMaxQ + 1) * sizeof(unsigned), s->stream);
   // padding columns must read as zero
   cudaMemsetAsync(s->rows, 0, (size_t)capacity * s->ld * elem_size(dtype), s->stream);
   cudaStreamSynchronize(s->stream);
@@ -550,13 +552,16 @@ static int scan_launch(int dtype, const ScanParams& p, int64_t nq, int n_sm, cud
   return fail(RAGB_EINVAL, "bad dtype %d", dtype);
 }
 
+struct WaitSpec { const uint64_t* flags; int n; unsigned long long epoch; int* status; };
 static int merge_launch(const uint64_t* keys, int64_t nq, int n_lists, int kpad, int64_t stride_q, int64_t stride_p,
                         int k, float* out_scores, int64_t* out_ids, uint64_t* out_keys, cudaStream_t st,
-                        bool unsorted = false) {
+                        bool unsorted = false, const PeerOut* po = nullptr, const WaitSpec* w = nullptr) {
   if (nq == 0) return RAGB_OK;
-  MergeParams m;
+  MergeParams m = {};
   m.keys = keys; m.n_lists = n_lists; m.kpad = kpad; m.k = k; m.stride_q = stride_q; m.stride_p = stride_p;
   m.out_scores = out_scores; m.out_ids = out_ids; m.out_keys = out_keys; m.unsorted = unsorted ? 1 : 0;
+  if (po) m.peers = *po;
+  if (w) { m.wait_flags = w->flags; m.wait_n = w->n; m.wait_epoch = w->epoch; m.status = w->status; }
   const size_t smem = (size_t)kMergeWarps * listbuf_len(kpad) * sizeof(uint64_t);
   if (smem > 48 * 1024) CU_TRY(cudaFuncSetAttribute(merge_topk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   merge_topk_kernel<<<(unsigned)nq, kMergeThreads, smem, st>>>(m);
@@ -623,11 +628,11 @@ static int gemm_finish(ragb_store* s, const float* q, int64_t nq, int k, int kpa
                        uint64_t* out_keys, float* out_scores, int64_t* out_ids, cudaStream_t st, int k_sel = 0) {
   const bool rescore = !(flags & RAGB_NO_RESCORE);
   if (!rescore)
-    return merge_launch(parts, nq, splits, kpad, (int64_t)splits * kpad, kpad, k, out_scores, out_ids, out_keys, st);
+    return merge_launch(parts, nq, splits, kpad, (int64_t)splits * kpad, kpad, k, out_scores, out_ids, out_keys, st, false, &s->peer);
   RB_TRY(merge_launch(parts, nq, splits, kpad, (int64_t)splits * kpad, kpad, k_sel > k ? k_sel : k, nullptr, nullptr, tmp, st));
   if (s->dtype == RAGB_BF16) RB_TRY(rescore_launch<__nv_bfloat16>(s, q, nq, metric, flags, threshold, id_base, kpad, tmp, st));
   else RB_TRY(rescore_launch<__half>(s, q, nq, metric, flags, threshold, id_base, kpad, tmp, st));
-  return merge_launch(tmp, nq, 1, kpad, kpad, kpad, k, out_scores, out_ids, out_keys, st, /*unsorted=*/true);
+  return merge_launch(tmp, nq, 1, kpad, kpad, kpad, k, out_scores, out_ids, out_keys, st, /*unsorted=*/true, &s->peer);
 }
 
 // SM-pair kernel finish (merge.cuh: finish_chunks_kernel): fold the per-split CHUNK lists, score the 32 rows of every
@@ -637,11 +642,12 @@ static int gemm_finish_chunks(ragb_store* s, const float* q, int64_t nq, int k, 
                               const uint64_t* parts, int splits, uint64_t* out_keys, float* out_scores, int64_t* out_ids,
                               cudaStream_t st) {
   static_assert(kFinishChunkRows == kChunkRows, "epilogue and finish kernel disagree on the chunk size");
-  FinishParams f;
+  FinishParams f = {};
   f.parts = parts; f.n_lists = splits; f.kpad = kpad; f.k_sel = k_sel; f.k = k;
   f.X = s->rows; f.ld = s->ld; f.dim = s->dim; f.q = q; f.metric = metric; f.flags = flags; f.threshold = threshold;
   f.row_begin = rb; f.row_end = re; f.valid = valid; f.id_base = id_base;
   f.out_scores = out_scores; f.out_ids = out_ids; f.out_keys = out_keys;
+  f.peers = s->peer;
   const size_t smem = finish_smem_bytes(splits, kpad);
   if (smem > 200 * 1024) return fail(RAGB_EUNSUPPORTED, "internal: %d splits x kpad %d do not fit the finish kernel", splits, kpad);
   if (s->dtype == RAGB_BF16) {
@@ -911,7 +917,7 @@ static int search_core(ragb_store* s, const float* q, int64_t nq, int k, int met
   if (nq == 0) return RAGB_OK;
   const int kpad = kpad_of(k);
   if (re - rb <= 0)  // empty store / empty window: RAGResult([], []) (:517-521)
-    return merge_launch(nullptr, nq, 0, kpad, 0, 0, k, out_scores, out_ids, out_keys, st);
+    return merge_launch(nullptr, nq, 0, kpad, 0, 0, k, out_scores, out_ids, out_keys, st, false, &s->peer);
   if (gemm_eligible(s, nq, k, flags))
     return gemm_search(s, q, nq, k, metric, threshold, flags, rb, re, valid, id_base, out_keys, out_scores, out_ids, st);
   ScanParams p;
@@ -919,6 +925,8 @@ static int search_core(ragb_store* s, const float* q, int64_t nq, int k, int met
   p.q = q; p.ld_q = s->dim; p.metric = metric; p.flags = flags; p.threshold = threshold;
   p.k = k; p.kpad = kpad; p.id_base = id_base; p.out = nullptr;
   p.tickets = nullptr; p.out_scores = nullptr; p.out_ids = nullptr; p.out_keys = nullptr;
+  p.peers = PeerOut{};
+  if (s->peer.n && nq > kScanMaxQ) return fail(RAGB_EUNSUPPORTED, "peer exchange supports at most %lld queries per call on the scan path", (long long)kScanMaxQ);
   // the grid y dimension caps one launch at 65535 queries
   int n_lists = 0;
   RB_TRY(scan_launch(s->dtype, p, nq, s->n_sm, st, &n_lists));  // sizing
@@ -932,6 +940,7 @@ static int search_core(ragb_store* s, const float* q, int64_t nq, int k, int met
     p.q = q + (size_t)q0 * s->dim;
     p.out = (uint64_t*)s->ws;
     p.tickets = fused ? s->tickets : nullptr;
+    if (fused) p.peers = s->peer;
     p.out_scores = out_scores ? out_scores + q0 * k : nullptr;
     p.out_ids = out_ids ? out_ids + q0 * k : nullptr;
     p.out_keys = out_keys ? out_keys + q0 * kpad : nullptr;
@@ -941,7 +950,7 @@ static int search_core(ragb_store* s, const float* q, int64_t nq, int k, int met
     }
     if (!fused)
       RB_TRY(merge_launch((const uint64_t*)s->ws, m, n_lists, kpad, (int64_t)n_lists * kpad, kpad, k, p.out_scores,
-                          p.out_ids, p.out_keys, st));
+                          p.out_ids, p.out_keys, st, false, &s->peer));
   }
   return RAGB_OK;
 }
@@ -957,6 +966,54 @@ extern "C" int ragb_search_keys_dev(ragb_store* s, const float* q, int64_t nq, i
   RB_TRY(search_core(s, q, nq, k, metric, threshold, flags, row_begin, row_end, valid, id_base, out_keys, nullptr, nullptr, st));
   if (!stream) CU_TRY(cudaStreamSynchronize(st));
   return RAGB_OK;
+}
+
+// ---- candidate exchange over peer memory -------------------------------------------------------------------
+static_assert(kMaxPeers == RAGB_MAX_PEERS, "PeerOut and ragb_exchange disagree on the rank limit");
+static int check_exchange(const ragb_exchange* x) {
+  if (!x) return fail(RAGB_EINVAL, "exchange is NULL");
+  if (x->world < 1 || x->world > RAGB_MAX_PEERS || x->rank < 0 || x->rank >= x->world)
+    return fail(RAGB_EINVAL, "bad exchange: world %d rank %d (at most %d ranks)", x->world, x->rank, RAGB_MAX_PEERS);
+  if (x->epoch == 0) return fail(RAGB_EINVAL, "exchange epoch must be > 0");
+  for (int r = 0; r < x->world; ++r)
+    if (!x->keys[r] || !x->flags[r]) return fail(RAGB_EINVAL, "exchange buffer of rank %d is NULL", r);
+  return RAGB_OK;
+}
+
+extern "C" int ragb_search_scatter_dev(ragb_store* s, const float* q, int64_t nq, int k, int metric, float threshold,
+                                       int flags, int64_t row_begin, int64_t row_end, const uint8_t* valid,
+                                       uint32_t id_base, const ragb_exchange* x, void* stream) {
+  RB_TRY(check_search_args(s, q, nq, k, metric, &row_begin, &row_end));
+  RB_TRY(check_exchange(x));
+  if (nq == 0) return fail(RAGB_EINVAL, "peer exchange needs at least one query");
+  std::lock_guard<std::mutex> ls(s->search_mu);
+  ON_DEVICE(s->device);
+  cudaStream_t st = stream ? (cudaStream_t)stream : s->stream;
+  const int kpad = kpad_of(k);
+  PeerOut po = {};
+  po.n = x->world; po.epoch = x->epoch; po.done = s->tickets + kScanMaxQ;
+  for (int r = 0; r < x->world; ++r) {
+    po.keys[r] = x->keys[r] + (size_t)x->rank * nq * kpad;  // this rank's [nq][kpad] slot in rank r's buffer
+    po.flag[r] = x->flags[r] + x->rank;
+  }
+  s->peer = po;
+  const int rc = search_core(s, q, nq, k, metric, threshold, flags, row_begin, row_end, valid, id_base, nullptr, nullptr, nullptr, st);
+  s->peer = PeerOut{};
+  if (rc != RAGB_OK) return rc;
+  if (!stream) CU_TRY(cudaStreamSynchronize(st));
+  return RAGB_OK;
+}
+
+extern "C" int ragb_gather_merge_dev(int device, const ragb_exchange* x, int64_t nq, int k, float* out_scores,
+                                     int64_t* out_ids, int* out_status, void* stream) {
+  RB_TRY(check_exchange(x));
+  if (nq <= 0 || k <= 0 || k > 1024) return fail(RAGB_EINVAL, "bad merge arguments");
+  if (!out_scores || !out_ids) return fail(RAGB_EINVAL, "output buffer is NULL");
+  ON_DEVICE(device);
+  const int kpad = kpad_of(k);
+  WaitSpec w = {x->flags[x->rank], x->world, x->epoch, out_status};
+  return merge_launch(x->keys[x->rank], nq, x->world, kpad, kpad, (int64_t)nq * kpad, k, out_scores, out_ids, nullptr,
+                      (cudaStream_t)stream, false, nullptr, &w);
 }
 
 extern "C" int ragb_search_dev(ragb_store* s, const float* q, int64_t nq, int k, int metric, float threshold, int flags,

@@ -34,6 +34,7 @@ struct ScanParams {
   float* out_scores;     // [nq][k] or null
   int64_t* out_ids;      // [nq][k] or null
   uint64_t* out_keys;    // [nq][kpad] or null (sorted keys, for the cross-GPU merge)
+  PeerOut peers;         // peers.n > 0 (needs tickets): the merging CTA also stores the keys into every rank's buffer
 };
 
 __device__ __forceinline__ float query_scale(const float* q, int dim, int metric, int lane) {
@@ -98,7 +99,10 @@ __device__ __forceinline__ void fused_final_merge(WarpTopK& tk, uint64_t* smem_l
     }
     if (p.out_keys)
       for (int i = lane; i < p.kpad; i += 32) p.out_keys[qi * p.kpad + i] = i < p.k ? tk.buf[i] : 0;
+    if (p.peers.n)
+      for (int i = lane; i < p.kpad; i += 32) peer_emit(p.peers, qi * p.kpad + i, i < p.k ? tk.buf[i] : 0);
   }
+  if (p.peers.n) peer_signal(p.peers, gridDim.y);  // one merging CTA per query
 }
 
 // G lanes per row, CPL 16-byte chunks per lane (row = G*CPL chunks), U row-slots in flight

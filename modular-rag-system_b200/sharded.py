@@ -65,20 +65,61 @@ def merge_keys_host(gathered: np.ndarray, k: int) -> Tuple[np.ndarray, np.ndarra
     return ids, sc
 
 
+class PeerBuffers:
+    """Gather buffers + arrival words of the peer-memory candidate exchange (include/ragb200.h, ragb_exchange).
+
+    Layout of every rank's block, in uint64 words: [16 arrival words | buffer 0 | buffer 1], each buffer
+    ``world x nq_cap x kpad`` keys; consecutive exchanges alternate between the two buffers.  ``ptrs[r]`` is the
+    address of rank r's block as mapped in THIS process (torch symmetric memory across processes; plain device
+    tensors when several "ranks" are emulated inside one process for tests)."""
+    HDR = 16
+
+    def __init__(self, ptrs, world: int, rank: int, nq_cap: int, kpad: int):
+        from ._lib import MAX_PEERS
+        if world > MAX_PEERS:
+            raise ValueError(f"peer exchange supports at most {MAX_PEERS} ranks, got {world}")
+        self.ptrs, self.world, self.rank, self.nq_cap, self.kpad = [int(p) for p in ptrs], world, rank, nq_cap, kpad
+        self.epoch = 0
+
+    @staticmethod
+    def words(world: int, nq_cap: int, kpad: int) -> int:
+        return PeerBuffers.HDR + 2 * world * nq_cap * kpad
+
+    def next_exchange(self):
+        """The ragb_exchange of the next epoch (all ranks call this in lock step)."""
+        from ._lib import Exchange
+        self.epoch += 1
+        x = Exchange()
+        x.world, x.rank, x.epoch = self.world, self.rank, self.epoch
+        off = 8 * (self.HDR + (self.epoch & 1) * self.world * self.nq_cap * self.kpad)
+        for r in range(self.world):
+            x.keys[r] = self.ptrs[r] + off
+            x.flags[r] = self.ptrs[r]
+        return x
+
+
 class ShardedSearcher:
     """Search a corpus whose rows are split over the ranks of a torch.distributed group.
 
     ``store`` is this rank's DeviceStore holding rows [row_base, row_base + len(store)).
     All ranks call ``search_dev`` with the same queries; every rank gets the full result.
-    """
 
-    def __init__(self, store, row_base: int, group=None):
+    exchange = "peer" (default on CUDA with world > 1): the last kernel of the local search stores its k
+    candidates per query straight into every rank's gather buffer over NVLink and signals; the merge kernel
+    waits for the signals — no collective launch.  exchange = "nccl": one all_gather_into_tensor + merge."""
+
+    def __init__(self, store, row_base: int, group=None, exchange: Optional[str] = None):
         import torch.distributed as dist
         self.store, self.row_base, self.group = store, int(row_base), group
         self.dist = dist
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        self.exchange = exchange or ("peer" if self.world > 1 else "nccl")
         self._keys = None
         self._gathered = None
+        self._peer = None      # PeerBuffers
+        self._peer_mem = None  # the symmetric allocation (kept alive)
+        self._status = None
 
     def _buffers(self, nq: int, kpad: int, device):
         import torch
@@ -87,17 +128,46 @@ class ShardedSearcher:
             self._gathered = torch.empty((self.world * nq, kpad), dtype=torch.int64, device=device)
         return self._keys, self._gathered
 
+    def _peer_buffers(self, nq: int, kpad: int, device):
+        """(Re)allocate the symmetric gather block; collective over the group (same nq, kpad on all ranks)."""
+        import torch
+        import torch.distributed._symmetric_memory as symm
+        if self._peer is not None and self._peer.nq_cap >= nq and self._peer.kpad == kpad:
+            return self._peer
+        torch.cuda.synchronize(device)
+        cap = max(nq, 1024)
+        mem = symm.empty(PeerBuffers.words(self.world, cap, kpad), dtype=torch.int64, device=device)
+        mem.zero_()
+        grp = self.group if self.group is not None else self.dist.group.WORLD
+        hdl = symm.rendezvous(mem, grp)
+        torch.cuda.synchronize(device)
+        self.dist.barrier(group=self.group)  # every block is zeroed before anybody writes into it
+        self._peer_mem = (mem, hdl)
+        self._peer = PeerBuffers(list(hdl.buffer_ptrs), self.world, self.rank, cap, kpad)
+        self._status = torch.zeros(1, dtype=torch.int32, device=device)
+        return self._peer
+
     def search_dev(self, q, k: int, metric: str = "ip", threshold: float = NEG_INF, clamp01: bool = False,
                    flags: int = 0):
         """q: CUDA fp32 [nq, dim], identical on all ranks -> (ids int64 [nq,k] GLOBAL rows, scores fp32 [nq,k])."""
-        from .store import kpad_of, merge_keys_dev
+        from .store import gather_merge_dev, kpad_of, merge_keys_dev
         kpad = kpad_of(k)
+        if self.world > 1 and self.exchange == "peer":
+            pb = self._peer_buffers(q.shape[0], kpad, q.device)
+            x = pb.next_exchange()
+            self.store.search_scatter_dev(q, k, x, metric, threshold, clamp01, id_base=self.row_base, flags=flags)
+            return gather_merge_dev(x, q.shape[0], k, self.store.device, status=self._status)
         keys, gathered = self._buffers(q.shape[0], kpad, q.device)
         self.store.search_keys_dev(q, k, metric, threshold, clamp01, id_base=self.row_base, flags=flags, out=keys)
         if self.world == 1:
             return merge_keys_dev(keys.unsqueeze(0), k, self.store.device)
         self.dist.all_gather_into_tensor(gathered, keys, group=self.group)
         return merge_keys_dev(gathered.view(self.world, q.shape[0], kpad), k, self.store.device)
+
+    def check(self) -> None:
+        """Raise if a merge ever timed out waiting for a rank (peer exchange only); synchronises."""
+        if self._status is not None and int(self._status.item()) != 0:
+            raise RuntimeError("peer exchange: a rank's candidates did not arrive within the kernel's timeout")
 
     def search(self, q: np.ndarray, k: int, metric: str = "ip", threshold: float = NEG_INF, clamp01: bool = False,
                flags: int = 0) -> Tuple[np.ndarray, np.ndarray]:

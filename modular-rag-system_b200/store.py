@@ -233,6 +233,14 @@ class DeviceStore:
         return keys
 
 
+    def search_scatter_dev(self, q, k: int, exchange, metric: str = "ip", threshold: float = NEG_INF,
+                           clamp01: bool = False, id_base: int = 0, flags: int = 0) -> None:
+        """Local top-k whose last kernel stores the sorted keys into every rank's gather buffer (peer memory)
+        and publishes the epoch; `exchange` is a _lib.Exchange.  Pair with gather_merge_dev()."""
+        fl = int(flags) | (CLAMP01 if clamp01 else 0)
+        check(self._lib.ragb_search_scatter_dev(self._h, q.data_ptr(), q.shape[0], int(k), _METRICS[metric], float(threshold),
+                                                fl, 0, -1, None, int(id_base), C.byref(exchange), _cur_stream(self.device)))
+
     # -- measurement ------------------------------------------------------------ #
     def profile(self, enable: bool = True) -> None:
         """Bracket the dominant kernel of every later search with CUDA events (bench.py's roofline leg)."""
@@ -257,6 +265,18 @@ def merge_keys_dev(keys, k: int, device: int):
     scores = torch.empty((nq, k), dtype=torch.float32, device=keys.device)
     check(lib().ragb_merge_keys_dev(int(device), keys.data_ptr(), nq, n_lists, kpad, kpad, nq * kpad, int(k),
                                     scores.data_ptr(), ids.data_ptr(), _cur_stream(device)))
+    return ids, scores
+
+
+def gather_merge_dev(exchange, nq: int, k: int, device: int, status=None, out=None):
+    """Wait until every rank's keys of `exchange.epoch` have arrived in this rank's gather buffer, merge them.
+    status: optional int32 CUDA tensor [1], set to 1 by the kernel if a rank did not arrive within ~2 s."""
+    import torch
+    dev = torch.device("cuda", device)
+    ids, scores = out if out is not None else (torch.empty((nq, k), dtype=torch.int64, device=dev),
+                                               torch.empty((nq, k), dtype=torch.float32, device=dev))
+    check(lib().ragb_gather_merge_dev(int(device), C.byref(exchange), int(nq), int(k), scores.data_ptr(), ids.data_ptr(),
+                                      status.data_ptr() if status is not None else None, _cur_stream(device)))
     return ids, scores
 
 
