@@ -160,7 +160,7 @@ class ClockSampler:
             f = tempfile.NamedTemporaryFile("w", suffix=".csv", delete=False)
             self.path = f.name
             self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                          "-lms", "100", "-i", str(self.index)], stdout=f, stderr=subprocess.DEVNULL)
+                                          "-lms", "20", "-i", str(self.index)], stdout=f, stderr=subprocess.DEVNULL)
         except Exception:
             self.proc = None
         return self
@@ -304,6 +304,7 @@ def run_b200(args):
     torch.cuda.set_device(local)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")  # keep stdout to the one JSON line (NCCL logs its version)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     pk, pk_src = peaks()
     wl = WORKLOADS[args.workload]

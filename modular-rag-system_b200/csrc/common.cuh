@@ -52,12 +52,14 @@ struct PeerOut {
   unsigned* done;                   // CTA completion counter of this launch (zero between launches)
   unsigned long long epoch;
   int n;                            // ranks (0 = exchange off)
+  int signal;                       // 0: store keys only (an earlier launch of a split batch; the last one signals)
 };
 __device__ __forceinline__ void peer_emit(const PeerOut& po, int64_t idx, uint64_t key) {
   for (int r = 0; r < po.n; ++r) po.keys[r][idx] = key;
 }
 // every thread of the CTA calls it after its peer_emit()s; n_ctas = CTAs that will call it in this launch
 __device__ __forceinline__ void peer_signal(const PeerOut& po, unsigned n_ctas) {
+  if (!po.signal) return;
   __threadfence_system();
   __syncthreads();
   if (threadIdx.x == 0) {

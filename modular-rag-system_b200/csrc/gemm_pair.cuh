@@ -51,11 +51,15 @@ __device__ __forceinline__ void tc_commit_pair(uint64_t* bar) {  // arrives on b
                "h"((uint16_t)3)
                : "memory");
 }
-__device__ __forceinline__ void mbar_arrive_cta(uint64_t* bar, uint32_t cta) {  // arrive on CTA `cta`'s copy
+// Arrive on CTA `cta`'s copy of the barrier.  RELAXED on purpose: the arrival only says "my tcgen05.ld of this
+// accumulator have completed" (tcgen05.wait::ld + fence::before_thread_sync precede it); no memory is published.
+// A release here costs an ERRBAR + CCTL.IVALL per tile and has to drain the candidate stores (global memory for
+// k > 32) before the MMA warp may reuse the accumulator — 13 % of the kernel's stall samples at top-100.
+__device__ __forceinline__ void mbar_arrive_cta(uint64_t* bar, uint32_t cta) {
   asm volatile(
       "{\n\t.reg .b32 ra;\n\t"
       "mapa.shared::cluster.u32 ra, %0, %1;\n\t"
-      "mbarrier.arrive.release.cluster.shared::cluster.b64 _, [ra];\n\t}" ::"r"(smem_u32(bar)),
+      "mbarrier.arrive.relaxed.cluster.shared::cluster.b64 _, [ra];\n\t}" ::"r"(smem_u32(bar)),
       "r"(cta)
       : "memory");
 }
