@@ -124,6 +124,22 @@ int ragb_search_dev(ragb_store* s, const float* q, int64_t nq, int k, int metric
                     int flags, int64_t row_begin, int64_t row_end, const uint8_t* valid,
                     float* out_scores, int64_t* out_ids, void* stream);
 
+/* ---- candidate-set policy on the device ---------------------------------------
+ * The SQL of _search_sqlite (ollama_rag_system.py:462-477: WHERE source IN (...) ORDER BY timestamp DESC
+ * LIMIT 1000), the NULL-embedding skip (:485-492) and INSERT OR REPLACE (:351), evaluated by kernels over
+ * two per-row arrays kept next to the rows: flags (bit 0 = live, bit 1 = has an embedding; default 3) and a
+ * 16-bit source code (default 0).  ragb_store_build_filter leaves a per-row mask in the store — match =
+ * live and (n_codes == 0 or src_allowed[code]); only the LAST `window` matches in row order stay
+ * (window < 0: all; exact for the reference when timestamps do not decrease in row order); rows without an
+ * embedding are never valid — and returns the number of rows the SQL would have returned
+ * (total_documents_searched, :520).  Pass RAGB_STORE_FILTER as `valid` to any search entry point to use it.
+ * Adding rows or changing metadata invalidates the mask. */
+#define RAGB_STORE_FILTER ((const uint8_t*)(uintptr_t)1)
+int ragb_store_set_meta(ragb_store* s, int64_t row0, int64_t n, const uint8_t* flags,
+                        const uint16_t* src); /* host arrays; NULL = leave unchanged */
+int ragb_store_build_filter(ragb_store* s, const uint8_t* src_allowed, int n_codes, int64_t window,
+                            int64_t* out_total);
+
 /* ---- measurement ------------------------------------------------------------
  * While enabled, every search call brackets its dominant kernel (the scan for the
  * bandwidth-bound path, the tcgen05 kernel for the batched path) with CUDA events on the

@@ -23,6 +23,7 @@ _vp, _i, _i64, _f = C.c_void_p, C.c_int, C.c_int64, C.c_float
 _pi64 = C.POINTER(C.c_int64)
 
 MAX_PEERS = 8
+STORE_FILTER = C.c_void_p(1)   # RAGB_STORE_FILTER: "use the mask ragb_store_build_filter left in the store"
 
 
 class Exchange(C.Structure):
@@ -59,6 +60,8 @@ SIGNATURES = {
     "ragb_store_get_rows": (_i, [_vp, _i64, _i64, _vp, _vp]),
     "ragb_search": (_i, [_vp, _vp, _i64, _i, _i, _f, _i, _i64, _i64, _vp, _vp, _vp]),
     "ragb_search_dev": (_i, [_vp, _vp, _i64, _i, _i, _f, _i, _i64, _i64, _vp, _vp, _vp, _vp]),
+    "ragb_store_set_meta": (_i, [_vp, _i64, _i64, _vp, _vp]),
+    "ragb_store_build_filter": (_i, [_vp, _vp, _i, _i64, _pi64]),
     "ragb_store_profile": (_i, [_vp, _i]),
     "ragb_store_profile_read": (_i, [_vp, C.POINTER(C.c_double), _pi64]),
     "ragb_kpad": (_i, [_i]),

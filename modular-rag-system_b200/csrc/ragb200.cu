@@ -17,6 +17,7 @@
 #include "gemm_topk.cuh"
 #include "gemm_ts.cuh"
 #include "gemm_pair.cuh"
+#include "filter.cuh"
 #include "ingest.cuh"
 #include "merge.cuh"
 #include "scan.cuh"
@@ -77,6 +78,14 @@ struct ragb_store {
   unsigned* tickets = nullptr;  // [kScanMaxQ + 1] zero between launches: last-CTA final merge of the scan (scan.cuh);
                                 // the extra word counts finished CTAs for the peer exchange signal
   PeerOut peer = {};            // set for the duration of ragb_search_scatter_dev (guarded by search_mu)
+  // candidate-set policy on the device (filter.cuh); guarded by search_mu
+  uint8_t* meta_flags = nullptr;   // [meta_cap] bit0 live, bit1 has embedding (default 3)
+  uint16_t* meta_src = nullptr;    // [meta_cap] source code (default 0)
+  int64_t meta_cap = 0;
+  uint8_t* filter = nullptr;       // [meta_cap] valid bytes built by ragb_store_build_filter
+  int64_t filter_n = -1;           // rows the filter covers (-1 = none built)
+  void* filter_aux = nullptr;      // counts | result | src_allowed
+  size_t filter_aux_bytes = 0;
   // ingest staging (guarded by add_mu)
   void* stage_dev = nullptr;
   size_t stage_dev_bytes = 0;
@@ -193,6 +202,7 @@ extern "C" int ragb_store_destroy(ragb_store* s) {
     cudaStreamSynchronize(s->stream);
     gemm_state_free(&s->gemm);
     cudaFree(s->rows); cudaFree(s->norms); cudaFree(s->ws); cudaFree(s->stage_dev); cudaFree(s->io); cudaFree(s->tickets);
+    cudaFree(s->meta_flags); cudaFree(s->meta_src); cudaFree(s->filter); cudaFree(s->filter_aux);
     if (s->stage_host) cudaFreeHost(s->stage_host);
     if (s->pin) cudaFreeHost(s->pin);
     for (auto& ev : s->prof_events) { cudaEventDestroy(ev.first); cudaEventDestroy(ev.second); }
@@ -232,6 +242,7 @@ extern "C" int ragb_store_clear(ragb_store* s) {
   std::lock_guard<std::mutex> la(s->add_mu);
   std::lock_guard<std::mutex> ls(s->search_mu);
   s->n.store(0);
+  s->filter_n = -1;
   return RAGB_OK;
 }
 extern "C" int64_t ragb_store_size(const ragb_store* s) { return s ? s->n.load(std::memory_order_acquire) : 0; }
@@ -957,6 +968,8 @@ static int check_search_args(ragb_store* s, const void* q, int64_t nq, int k, in
   return RAGB_OK;
 }
 
+static int resolve_valid(ragb_store* s, const uint8_t** valid, int64_t row_end, bool* is_store_filter);
+
 // core: device pointers, caller holds search_mu and has selected the device.
 // Writes sorted keys (out_keys, kpad per query) and/or decoded (out_scores, out_ids).
 static int search_core(ragb_store* s, const float* q, int64_t nq, int k, int metric, float threshold, int flags,
@@ -1011,8 +1024,93 @@ extern "C" int ragb_search_keys_dev(ragb_store* s, const float* q, int64_t nq, i
   std::lock_guard<std::mutex> ls(s->search_mu);
   ON_DEVICE(s->device);
   cudaStream_t st = stream ? (cudaStream_t)stream : s->stream;
+  bool sf;
+  RB_TRY(resolve_valid(s, &valid, row_end, &sf));
   RB_TRY(search_core(s, q, nq, k, metric, threshold, flags, row_begin, row_end, valid, id_base, out_keys, nullptr, nullptr, st));
   if (!stream) CU_TRY(cudaStreamSynchronize(st));
+  return RAGB_OK;
+}
+
+// ---- candidate-set policy on the device (filter.cuh) ----------------------------------------------------------
+static int meta_reserve(ragb_store* s, int64_t need) {  // caller holds search_mu, device selected
+  if (need <= s->meta_cap) return RAGB_OK;
+  const int64_t cap = std::max<int64_t>(std::max<int64_t>(need, s->capacity), 2 * s->meta_cap);
+  uint8_t* fl = nullptr; uint16_t* sr = nullptr; uint8_t* fi = nullptr;
+  if (cudaMalloc(&fl, cap) != cudaSuccess || cudaMalloc(&sr, cap * 2) != cudaSuccess || cudaMalloc(&fi, cap) != cudaSuccess) {
+    cudaFree(fl); cudaFree(sr); cudaFree(fi);
+    return fail(RAGB_ENOMEM, "cudaMalloc of %lld rows of filter metadata failed", (long long)cap);
+  }
+  cudaMemsetAsync(fl, 3, cap, s->stream);       // rows nobody described are live and searchable
+  cudaMemsetAsync(sr, 0, cap * 2, s->stream);
+  if (s->meta_cap) {
+    cudaMemcpyAsync(fl, s->meta_flags, s->meta_cap, cudaMemcpyDeviceToDevice, s->stream);
+    cudaMemcpyAsync(sr, s->meta_src, s->meta_cap * 2, cudaMemcpyDeviceToDevice, s->stream);
+  }
+  CU_TRY(cudaStreamSynchronize(s->stream));
+  cudaFree(s->meta_flags); cudaFree(s->meta_src); cudaFree(s->filter);
+  s->meta_flags = fl; s->meta_src = sr; s->filter = fi; s->meta_cap = cap; s->filter_n = -1;
+  return RAGB_OK;
+}
+
+extern "C" int ragb_store_set_meta(ragb_store* s, int64_t row0, int64_t n, const uint8_t* flags, const uint16_t* src) {
+  if (!s) return fail(RAGB_EINVAL, "store is NULL");
+  if (row0 < 0 || n < 0 || row0 + n > s->n.load()) return fail(RAGB_EINVAL, "rows [%lld,%lld) out of range", (long long)row0, (long long)(row0 + n));
+  if (n == 0) return RAGB_OK;
+  std::lock_guard<std::mutex> ls(s->search_mu);
+  ON_DEVICE(s->device);
+  RB_TRY(meta_reserve(s, row0 + n));
+  if (flags) CU_TRY(cudaMemcpyAsync(s->meta_flags + row0, flags, (size_t)n, cudaMemcpyHostToDevice, s->stream));
+  if (src) CU_TRY(cudaMemcpyAsync(s->meta_src + row0, src, (size_t)n * 2, cudaMemcpyHostToDevice, s->stream));
+  CU_TRY(cudaStreamSynchronize(s->stream));
+  s->filter_n = -1;
+  return RAGB_OK;
+}
+
+extern "C" int ragb_store_build_filter(ragb_store* s, const uint8_t* src_allowed, int n_codes, int64_t window,
+                                       int64_t* out_total) {
+  if (!s) return fail(RAGB_EINVAL, "store is NULL");
+  if (n_codes < 0 || n_codes > 65536 || (n_codes && !src_allowed)) return fail(RAGB_EINVAL, "bad source table");
+  std::lock_guard<std::mutex> ls(s->search_mu);
+  ON_DEVICE(s->device);
+  const int64_t n = s->n.load(std::memory_order_acquire);
+  if (out_total) *out_total = 0;
+  s->filter_n = -1;
+  if (n == 0) { s->filter_n = 0; return RAGB_OK; }
+  RB_TRY(meta_reserve(s, n));
+  const int n_ctas = (int)((n + kFilterRowsPerCta - 1) / kFilterRowsPerCta);
+  const size_t counts_b = ((size_t)n_ctas * 4 + 15) / 16 * 16;
+  RB_TRY(grow(&s->filter_aux, &s->filter_aux_bytes, counts_b + 32 + 65536, false));
+  FilterParams p;
+  p.flags = s->meta_flags; p.src = s->meta_src; p.n = n; p.window = window; p.valid = s->filter;
+  p.counts = (unsigned*)s->filter_aux;
+  p.result = (int64_t*)((char*)s->filter_aux + counts_b);
+  uint8_t* allowed_dev = (uint8_t*)s->filter_aux + counts_b + 32;
+  p.src_allowed = n_codes ? allowed_dev : nullptr; p.n_codes = n_codes;
+  if (n_codes) CU_TRY(cudaMemcpyAsync(allowed_dev, src_allowed, (size_t)n_codes, cudaMemcpyHostToDevice, s->stream));
+  filter_mark_kernel<<<n_ctas, kFilterThreads, 0, s->stream>>>(p);
+  LAUNCHED();
+  filter_cut_kernel<<<1, 1024, 0, s->stream>>>(p, n_ctas);
+  LAUNCHED();
+  if (window >= 0) {
+    filter_window_kernel<<<n_ctas, kFilterThreads, 0, s->stream>>>(p);
+    LAUNCHED();
+  }
+  int64_t res[3] = {0, 0, 0};
+  CU_TRY(cudaMemcpyAsync(res, p.result, sizeof(res), cudaMemcpyDeviceToHost, s->stream));
+  CU_TRY(cudaStreamSynchronize(s->stream));
+  if (out_total) *out_total = res[0];
+  s->filter_n = n;
+  return RAGB_OK;
+}
+
+// valid == RAGB_STORE_FILTER: use the mask ragb_store_build_filter left in the store
+static int resolve_valid(ragb_store* s, const uint8_t** valid, int64_t row_end, bool* is_store_filter) {
+  *is_store_filter = false;
+  if (*valid != RAGB_STORE_FILTER) return RAGB_OK;
+  if (s->filter_n < 0) return fail(RAGB_EINVAL, "RAGB_STORE_FILTER: no filter built (ragb_store_build_filter), or rows/metadata changed since");
+  if (row_end > s->filter_n) return fail(RAGB_EINVAL, "RAGB_STORE_FILTER covers %lld rows, search asks for %lld: rebuild the filter", (long long)s->filter_n, (long long)row_end);
+  *valid = s->filter;
+  *is_store_filter = true;
   return RAGB_OK;
 }
 
@@ -1044,6 +1142,8 @@ extern "C" int ragb_search_scatter_dev(ragb_store* s, const float* q, int64_t nq
     po.keys[r] = x->keys[r] + (size_t)x->rank * nq * kpad;  // this rank's [nq][kpad] slot in rank r's buffer
     po.flag[r] = x->flags[r] + x->rank;
   }
+  bool sf;
+  RB_TRY(resolve_valid(s, &valid, row_end, &sf));
   s->peer = po;
   const int rc = search_core(s, q, nq, k, metric, threshold, flags, row_begin, row_end, valid, id_base, nullptr, nullptr, nullptr, st);
   s->peer = PeerOut{};
@@ -1072,6 +1172,8 @@ extern "C" int ragb_search_dev(ragb_store* s, const float* q, int64_t nq, int k,
   std::lock_guard<std::mutex> ls(s->search_mu);
   ON_DEVICE(s->device);
   cudaStream_t st = stream ? (cudaStream_t)stream : s->stream;
+  bool sf;
+  RB_TRY(resolve_valid(s, &valid, row_end, &sf));
   RB_TRY(search_core(s, q, nq, k, metric, threshold, flags, row_begin, row_end, valid, 0, nullptr, out_scores, out_ids, st));
   if (!stream) CU_TRY(cudaStreamSynchronize(st));
   return RAGB_OK;
@@ -1086,6 +1188,10 @@ extern "C" int ragb_search(ragb_store* s, const float* q, int64_t nq, int k, int
   ON_DEVICE(s->device);
   // per-call device buffer: q | scores | ids | valid ; pinned mirror of the first three
   const size_t qb = (size_t)nq * s->dim * 4, sb = (size_t)nq * k * 4, ib = (size_t)nq * k * 8;
+  bool store_filter;
+  RB_TRY(resolve_valid(s, &valid, row_end, &store_filter));  // the store's own mask is already on the device
+  const uint8_t* valid_dev = store_filter ? valid : nullptr;
+  if (store_filter) valid = nullptr;
   const size_t vb = valid ? (size_t)row_end : 0;
   auto al = [](size_t x) { return (x + 255) / 256 * 256; };
   const size_t o_s = al(qb), o_i = o_s + al(sb), o_v = o_i + al(ib);
@@ -1097,7 +1203,7 @@ extern "C" int ragb_search(ragb_store* s, const float* q, int64_t nq, int k, int
   CU_TRY(cudaMemcpyAsync(d, h, qb, cudaMemcpyHostToDevice, s->stream));
   if (valid) CU_TRY(cudaMemcpyAsync(d + o_v, valid, vb, cudaMemcpyHostToDevice, s->stream));
   RB_TRY(search_core(s, (const float*)d, nq, k, metric, threshold, flags, row_begin, row_end,
-                     valid ? (const uint8_t*)(d + o_v) : nullptr, 0, nullptr, (float*)(d + o_s), (int64_t*)(d + o_i), s->stream));
+                     valid ? (const uint8_t*)(d + o_v) : valid_dev, 0, nullptr, (float*)(d + o_s), (int64_t*)(d + o_i), s->stream));
   CU_TRY(cudaMemcpyAsync(h + o_s, d + o_s, o_v - o_s, cudaMemcpyDeviceToHost, s->stream));
   CU_TRY(cudaStreamSynchronize(s->stream));
   memcpy(out_scores, h + o_s, sb);

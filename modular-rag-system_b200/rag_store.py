@@ -136,6 +136,10 @@ class B200VectorStore:
         self._row_of: Dict[str, int] = {}
         self._src_code: Dict[str, int] = {}
         self._monotone = True                         # timestamps non-decreasing in row order
+        self._device_filter = True                    # candidate-set policy evaluated on the device (filter.cuh)
+        self._meta_version = 0
+        self._filter_key = None                       # (meta version, sources, window) of the mask now in the store
+        self._filter_total = 0
         self._init_sqlite_fallback()
         self._rebuild_from_sqlite()
         print(f"✅ RAG Vector Store initialized: {storage_path}")
@@ -201,6 +205,7 @@ class B200VectorStore:
                     self._store = DeviceStore(real, self.dtype, max(self._capacity0, n_old + len(items)), self.device)
                     if n_old:
                         self._store.add(np.zeros((n_old, real), np.float32))
+                        self._push_meta(0, n_old, [])
                     self._dim_is_placeholder = False
                     dim = real
             X = np.zeros((len(items), dim), np.float32)
@@ -214,11 +219,13 @@ class B200VectorStore:
             first = self._store.add(X)
             assert first == self._n
             self._grow_meta(self._n + len(items))
+            replaced: List[int] = []
             for i, (doc_id, _, ts, source) in enumerate(items):
                 r = first + i
                 old = self._row_of.get(doc_id)
                 if old is not None:
                     self._live[old] = False  # INSERT OR REPLACE (:351)
+                    replaced.append(old)
                 self._row_of[doc_id] = r
                 self.document_mapping[r] = doc_id
                 t = float(ts) if ts is not None else 0.0
@@ -229,6 +236,20 @@ class B200VectorStore:
                 self._live[r] = True
                 self._has[r] = has[i]
             self._n += len(items)
+            self._meta_version += 1
+            self._push_meta(first, len(items), replaced)
+
+    def _push_meta(self, first: int, m: int, replaced: Sequence[int]) -> None:
+        """Mirror live / has-embedding / source of the new rows (and the rows they replaced) onto the device, where
+        the candidate-set policy is evaluated (csrc/filter.cuh)."""
+        if len(self._src_code) > 65535:
+            self._device_filter = False  # more sources than 16-bit codes: host-built masks from here on
+            return
+        flags = self._live[first:first + m].astype(np.uint8) | (self._has[first:first + m].astype(np.uint8) << 1)
+        self._store.set_meta(first, flags, self._src[first:first + m].astype(np.uint16))
+        for r in replaced:
+            if r < first:
+                self._store.set_meta(r, np.array([int(self._has[r]) << 1], np.uint8))
 
     # -- ingest (:307-321, :346-370, :372-386) ------------------------------------------------ #
     def add_document(self, document) -> bool:
@@ -306,36 +327,122 @@ class B200VectorStore:
         results.retrieval_time = time.time() - start_time
         return results
 
-    def _search_device(self, query, query_embedding):
-        Doc, Res = self._types
+    def _device_candidates(self, source_filters) -> int:
+        """Monotone timestamps: the SQL's WHERE / ORDER BY / LIMIT (:462-477) evaluated by kernels into the store's
+        own mask; returns total_documents_searched.  Cached until rows, metadata or the filter change."""
+        srcs = tuple(sorted(set(source_filters))) if source_filters else None
+        key = (self._meta_version, srcs, self.window)
+        if key != self._filter_key:
+            allowed = None
+            if srcs is not None:
+                allowed = np.zeros(max(len(self._src_code), 1), np.uint8)
+                for name in srcs:
+                    if name in self._src_code:
+                        allowed[self._src_code[name]] = 1
+            self._filter_total = self._store.build_filter(allowed, self.window)
+            self._filter_key = key
+        return self._filter_total
+
+    def _search_rows(self, Q: np.ndarray, k: int, thr: float, source_filters):
+        """Device search of host queries Q [nq, dim] under the reference's policy -> (ids [nq][<=k], scores, total)."""
         with self._lock:
             n, store = self._n, self._store
             if store is None or n == 0:
-                return Res(documents=[], similarities=[], total_documents_searched=0)
-            valid, total = self._candidate_rows(query.source_filters)
+                return None, None, 0
             monotone = self._monotone
+            if monotone and self._device_filter:
+                total = self._device_candidates(source_filters)
+                if total == 0 or k <= 0:
+                    return None, None, total
+                ids, sc = store.search(Q, min(k, 1024), "cosine", threshold=thr, clamp01=True, row_end=n, valid="filter")
+                return ids, sc, total
+            valid, total = self._candidate_rows(source_filters)
             ts = self._ts[:n].copy() if not monotone else None
-        k = int(query.max_results)
-        if not query_embedding or k <= 0 or not valid.any():  # :493 — nothing is scored without a query vector
-            return Res(documents=[], similarities=[], total_documents_searched=total)
-        q = np.asarray(query_embedding, dtype=np.float32)
-        thr = float(query.similarity_threshold)
+        if k <= 0 or not valid.any():
+            return None, None, total
         n_valid = int(valid.sum())
         kk = min(k, 1024)
+        v8 = valid.astype(np.uint8)
         while True:
-            ids, sc = store.search(q, kk, "cosine", threshold=thr, clamp01=True, row_end=n, valid=valid.astype(np.uint8))
-            ids, sc = ids[0], sc[0]
-            got = ids >= 0
-            ids, sc = ids[got], sc[got]
-            if monotone or len(ids) < kk or kk >= min(n_valid, 1024) or sc[kk - 1] < sc[min(k, kk) - 1]:
-                break  # the tie group at the cut is complete (or timestamps follow row order)
+            ids, sc = store.search(Q, kk, "cosine", threshold=thr, clamp01=True, row_end=n, valid=v8)
+            full = (ids[:, kk - 1] >= 0) & (sc[:, kk - 1] >= sc[:, min(k, kk) - 1])
+            if monotone or kk >= min(n_valid, 1024) or not full.any():
+                break  # the tie group at the cut is complete for every query (or timestamps follow row order)
             kk = min(1024, 2 * kk)
-        if not monotone and len(ids):  # reference order: score desc, then newer timestamp (:474, :512)
-            order = np.lexsort((-ids, -ts[ids], -sc.astype(np.float64)))
-            ids, sc = ids[order], sc[order]
-        ids, sc = ids[:k], sc[:k]
+        if not monotone:  # reference order: score desc, then newer timestamp (:474, :512)
+            out_i, out_s = np.full((len(ids), k), -1, np.int64), np.full((len(ids), k), -np.inf, np.float32)
+            for j in range(len(ids)):
+                g = ids[j] >= 0
+                ij, sj = ids[j][g], sc[j][g]
+                order = np.lexsort((-ij, -ts[ij], -sj.astype(np.float64)))[:k]
+                out_i[j, :len(order)], out_s[j, :len(order)] = ij[order], sj[order]
+            ids, sc = out_i, out_s
+        return ids[:, :k], sc[:, :k], total
+
+    def _search_device(self, query, query_embedding):
+        Doc, Res = self._types
+        k = int(query.max_results)
+        if not query_embedding:  # :493 — nothing is scored without a query vector
+            with self._lock:
+                total = 0 if self._store is None or self._n == 0 else self._candidate_rows(query.source_filters)[1]
+            return Res(documents=[], similarities=[], total_documents_searched=total)
+        q = np.asarray(query_embedding, dtype=np.float32)[None, :]
+        ids, sc, total = self._search_rows(q, k, float(query.similarity_threshold), query.source_filters)
+        if ids is None:
+            return Res(documents=[], similarities=[], total_documents_searched=total)
+        got = ids[0] >= 0
+        ids, sc = ids[0][got], sc[0][got]
         docs = self._fetch_documents([self.document_mapping[int(r)] for r in ids], Doc)
-        return Res(documents=docs, similarities=[float(s) for s in sc], total_documents_searched=total)
+        return Res(documents=docs, similarities=[float(x) for x in sc], total_documents_searched=total)
+
+    def search_many(self, queries: Sequence, embeddings: Optional[Sequence] = None) -> List[Any]:
+        """Batched ``search``: the queries of one call that share (max_results, similarity_threshold,
+        source_filters) go to the device as ONE batch (the tcgen05 kernel from 4 queries up), instead of the
+        caller looping over ``search`` (examples/llm_integration.py:54-59, rag_query_interface.py:287-311).
+        Returns one ``RAGResult`` per query, in order; same error convention as ``search``."""
+        Doc, Res = self._types
+        t0 = time.time()
+        out: List[Any] = [None] * len(queries)
+        groups: Dict[tuple, List[int]] = {}
+        embs: List[Optional[List[float]]] = []
+        for i, qy in enumerate(queries):
+            try:
+                e = embeddings[i] if embeddings is not None else self.embedding_generator.generate_embedding(qy.query_text)
+            except Exception as ex:
+                print(f"Device search error: {ex}")
+                e = None
+            embs.append(e)
+            dim = None if self._store is None else self._store.dim
+            if not e or dim is None or len(e) != dim:
+                # no vector / wrong length: the single-query path handles it (0.0 scores or nothing, :201-202, :493)
+                try:
+                    out[i] = self._search_device(qy, e) if e is not None else Res(documents=[], similarities=[])
+                except Exception as ex:
+                    print(f"Device search error: {ex}")
+                    out[i] = Res(documents=[], similarities=[])
+                continue
+            key = (int(qy.max_results), float(qy.similarity_threshold), tuple(sorted(qy.source_filters)) if qy.source_filters else None)
+            groups.setdefault(key, []).append(i)
+        for (k, thr, srcs), idx in groups.items():
+            try:
+                Q = np.asarray([embs[i] for i in idx], dtype=np.float32)
+                ids, sc, total = self._search_rows(Q, k, thr, list(srcs) if srcs else None)
+                for j, i in enumerate(idx):
+                    if ids is None:
+                        out[i] = Res(documents=[], similarities=[], total_documents_searched=total)
+                        continue
+                    got = ids[j] >= 0
+                    docs = self._fetch_documents([self.document_mapping[int(r)] for r in ids[j][got]], Doc)
+                    out[i] = Res(documents=docs, similarities=[float(x) for x in sc[j][got]], total_documents_searched=total)
+            except Exception as ex:
+                print(f"Device search error: {ex}")
+                for i in idx:
+                    out[i] = Res(documents=[], similarities=[])
+        dt = time.time() - t0
+        for i, r in enumerate(out):
+            r.query_embedding = embs[i]
+            r.retrieval_time = dt
+        return out
 
     def _fetch_documents(self, doc_ids: List[str], Doc) -> List[Any]:
         if not doc_ids:
@@ -392,5 +499,14 @@ def install(**store_kwargs) -> None:
         ok = self.vector_store.add_documents(docs)
         return [d.id for d, good in zip(docs, ok) if good]
 
+    def query_many(self, query_texts, context=None, max_results=None, source_filters=None) -> List[Any]:
+        """Batched ``RAGSystem.query`` (:683-721): same defaults, one device batch for all texts."""
+        cfg = self.config.get('retrieval', {}) if hasattr(self, 'config') else {}
+        qs = [ref.RAGQuery(query_text=t, context=context or {}, max_results=max_results or cfg.get('max_results', 5),
+                           similarity_threshold=cfg.get('similarity_threshold', 0.7), source_filters=source_filters)
+              for t in query_texts]
+        return self.vector_store.search_many(qs)
+
     ref.RAGVectorStore = _Installed
     ref.RAGSystem.add_documents = add_documents
+    ref.RAGSystem.query_many = query_many

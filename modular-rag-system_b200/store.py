@@ -192,7 +192,11 @@ class DeviceStore:
         ids = np.empty((nq, k), dtype=np.int64)
         scores = np.empty((nq, k), dtype=np.float32)
         vp = None
-        if valid is not None:
+        if isinstance(valid, str):
+            if valid != "filter":
+                raise ValueError('valid must be a byte mask or the string "filter" (the mask left by build_filter)')
+            vp = _lib.STORE_FILTER
+        elif valid is not None:
             valid = np.ascontiguousarray(valid, dtype=np.uint8)
             if valid.shape[0] < (len(self) if row_end < 0 else row_end):
                 raise ValueError("valid mask shorter than the row range")
@@ -216,7 +220,8 @@ class DeviceStore:
             ids, scores = out
         fl = int(flags) | (CLAMP01 if clamp01 else 0)
         check(self._lib.ragb_search_dev(self._h, q.data_ptr(), nq, int(k), _METRICS[metric], float(threshold), fl,
-                                        int(row_begin), int(row_end), None if valid is None else valid.data_ptr(),
+                                        int(row_begin), int(row_end),
+                                        None if valid is None else _lib.STORE_FILTER if isinstance(valid, str) else valid.data_ptr(),
                                         scores.data_ptr(), ids.data_ptr(), _cur_stream(self.device)))
         return ids, scores
 
@@ -232,6 +237,25 @@ class DeviceStore:
                                              0, -1, None, int(id_base), keys.data_ptr(), _cur_stream(self.device)))
         return keys
 
+
+    # -- candidate-set policy on the device (csrc/filter.cuh) -------------------- #
+    def set_meta(self, row0: int, flags: Optional[np.ndarray] = None, src: Optional[np.ndarray] = None) -> None:
+        """Per-row metadata of rows [row0, row0+n): flags uint8 (bit 0 live, bit 1 has an embedding; default 3) and
+        source codes uint16 (default 0) — what the SQL of ollama_rag_system.py:462-477 / :485-492 / :351 looks at."""
+        n = len(flags) if flags is not None else len(src)
+        f = None if flags is None else np.ascontiguousarray(flags, dtype=np.uint8)
+        c = None if src is None else np.ascontiguousarray(src, dtype=np.uint16)
+        check(self._lib.ragb_store_set_meta(self._h, int(row0), int(n), None if f is None else f.ctypes.data,
+                                            None if c is None else c.ctypes.data))
+
+    def build_filter(self, allowed_sources: Optional[np.ndarray] = None, window: Optional[int] = None) -> int:
+        """Evaluate (source IN ..., newest `window` rows, live, non-NULL) on the device into the store's own mask;
+        returns the number of rows the reference's SQL would have returned.  Search with ``valid="filter"``."""
+        tot = C.c_int64(0)
+        a = None if allowed_sources is None else np.ascontiguousarray(allowed_sources, dtype=np.uint8)
+        check(self._lib.ragb_store_build_filter(self._h, None if a is None else a.ctypes.data, 0 if a is None else len(a),
+                                                -1 if window is None else int(window), C.byref(tot)))
+        return int(tot.value)
 
     def search_scatter_dev(self, q, k: int, exchange, metric: str = "ip", threshold: float = NEG_INF,
                            clamp01: bool = False, id_base: int = 0, flags: int = 0) -> None:

@@ -136,3 +136,71 @@ def test_concurrent_writer_and_readers(tmp_path):
     assert not errors, errors[:3]
     assert vs.get_stats()["device_rows"] == 400
     vs.close()
+
+
+def test_device_filter_equals_numpy_policy():
+    """ragb_store_build_filter (source IN ..., newest-`window` matches in row order, live, non-NULL) against the
+    same policy written in numpy, over random metadata; the search under valid="filter" equals the search under
+    the numpy mask."""
+    from modular_rag_system_b200 import DeviceStore
+    rng = np.random.default_rng(5)
+    n, d = 23_456, 64
+    X = rng.standard_normal((n, d)).astype(np.float32)
+    s = DeviceStore(d, "fp16", n)
+    s.add(X)
+    live = rng.random(n) > 0.1
+    has = rng.random(n) > 0.05
+    src = rng.integers(0, 7, n).astype(np.uint16)
+    s.set_meta(0, live.astype(np.uint8) | (has.astype(np.uint8) << 1), src)
+    Q = rng.standard_normal((3, d)).astype(np.float32)
+    for allowed_codes, window in ((None, None), (None, 1000), ([1, 4], 1000), ([2], 5), ([6], 0), ([0, 1, 2, 3, 4, 5, 6], 20_000),
+                                  (None, 2048), (None, 2049), ([3], 100_000)):
+        allowed = None
+        match = live.copy()
+        if allowed_codes is not None:
+            allowed = np.zeros(7, np.uint8); allowed[allowed_codes] = 1
+            match &= np.isin(src, allowed_codes)
+        total = int(match.sum())
+        if window is not None and total > window:
+            keep = np.flatnonzero(match)[total - window:]
+            match = np.zeros(n, bool); match[keep] = True
+            total = window
+        got_total = s.build_filter(allowed, window)
+        assert got_total == total, (allowed_codes, window)
+        want = (match & has).astype(np.uint8)
+        a = s.search(Q, 10, "cosine", valid="filter")
+        b = s.search(Q, 10, "cosine", valid=want)
+        assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1]), (allowed_codes, window)
+    s.add(X[:10])  # new rows: the mask no longer covers the store
+    from modular_rag_system_b200 import RagbError
+    with pytest.raises(RagbError):
+        s.search(Q, 10, "cosine", valid="filter")
+
+
+def test_search_many_equals_looped_search(tmp_path):
+    """The batched front-end returns, per query, what the single-query entry point returns (ids, order, totals)."""
+    from modular_rag_system_b200 import B200VectorStore, RAGDocument, RAGQuery
+    rng = np.random.default_rng(9)
+    n, d = 3000, 96
+    X = rng.standard_normal((n, d))
+    vs = B200VectorStore(tmp_path / "many", window=None)
+    docs = [RAGDocument(id=f"d{i}", content=f"doc {i}", metadata={}, embedding=X[i].tolist(), timestamp=1000.0 + i,
+                        source=("a", "b", "c")[i % 3]) for i in range(n)]
+    assert all(vs.add_documents(docs))
+    qs = []
+    for j in range(40):
+        text = f"q{j}"
+        vs.embedding_generator.embedding_cache[text] = (X[(j * 37) % n] + 0.4 * rng.standard_normal(d)).tolist()
+        qs.append(RAGQuery(query_text=text, context={}, max_results=(3, 5, 7)[j % 3], similarity_threshold=(0.0, 0.3)[j % 2],
+                           source_filters=(None, ["a"], ["b", "c"])[j % 3]))
+    qs.append(RAGQuery(query_text="unknown text", context={}))  # no vector: empty result, no exception
+    many = vs.search_many(qs)
+    assert len(many) == len(qs)
+    for qy, m in zip(qs[:-1], many[:-1]):
+        one = vs.search(qy)
+        assert [x.id for x in one.documents] == [x.id for x in m.documents]
+        assert np.allclose(one.similarities, m.similarities, atol=1e-3)
+        assert one.total_documents_searched == m.total_documents_searched
+        if not qy.source_filters:
+            assert m.documents[0].id == f"d{(int(qy.query_text[1:]) * 37) % n}"
+    assert many[-1].documents == [] and many[-1].similarities == []
