@@ -108,6 +108,11 @@ int ragb_pool_norm_pack_dev(int device, const void* tok, int tok_dtype, const vo
                             int out_dtype, int64_t ld_out, float* out_norms, void* stream);
 /* copy rows [row0,row0+n) back to the host (packed elements, ld = dim) and their norms */
 int ragb_store_get_rows(ragb_store* s, int64_t row0, int64_t n, void* out_rows, float* out_norms);
+/* append rows that are already packed (store dtype, ld = dim — what ragb_store_get_rows returns) with their norms,
+ * verbatim: the restore half of the packed on-disk sidecar that replaces unpickling every BLOB of the
+ * reference's table (ollama_rag_system.py:358, :487) on open */
+int ragb_store_put_rows(ragb_store* s, const void* packed_rows, const float* norms, int64_t n,
+                        int64_t* out_first_row);
 
 /* ---- search ----------------------------------------------------------------
  * Replaces the scan / threshold / sort / slice of RAGVectorStore._search_sqlite

@@ -473,6 +473,26 @@ extern "C" int ragb_store_add_pooled(ragb_store* s, const void* tok, int tok_dty
   return RAGB_OK;
 }
 
+// append rows that are ALREADY packed (what ragb_store_get_rows returned): no arithmetic, bit-exact restore
+extern "C" int ragb_store_put_rows(ragb_store* s, const void* packed_rows, const float* norms, int64_t n,
+                                   int64_t* out_first_row) {
+  if (!s || ((!packed_rows || !norms) && n)) return fail(RAGB_EINVAL, "NULL argument");
+  std::lock_guard<std::mutex> la(s->add_mu);
+  ON_DEVICE(s->device);
+  int64_t first = 0;
+  RB_TRY(reserve_rows(s, n, &first));
+  if (n) {
+    const size_t es = elem_size(s->dtype);
+    CU_TRY(cudaMemcpy2DAsync(row_ptr(s, first), (size_t)s->ld * es, packed_rows, (size_t)s->dim * es, (size_t)s->dim * es,
+                             (size_t)n, cudaMemcpyHostToDevice, s->stream));
+    CU_TRY(cudaMemcpyAsync(s->norms + first, norms, (size_t)n * 4, cudaMemcpyHostToDevice, s->stream));
+    CU_TRY(cudaStreamSynchronize(s->stream));
+  }
+  s->n.store(first + n, std::memory_order_release);
+  if (out_first_row) *out_first_row = first;
+  return RAGB_OK;
+}
+
 extern "C" int ragb_store_get_rows(ragb_store* s, int64_t row0, int64_t n, void* out_rows, float* out_norms) {
   if (!s) return fail(RAGB_EINVAL, "store is NULL");
   if (row0 < 0 || n < 0 || row0 + n > s->n.load()) return fail(RAGB_EINVAL, "rows [%lld,%lld) out of range", (long long)row0, (long long)(row0 + n));

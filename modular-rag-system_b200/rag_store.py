@@ -141,7 +141,9 @@ class B200VectorStore:
         self._filter_key = None                       # (meta version, sources, window) of the mask now in the store
         self._filter_total = 0
         self._init_sqlite_fallback()
-        self._rebuild_from_sqlite()
+        self.restored_from = "sqlite"                 # "sidecar" when the packed rows came back from disk
+        if not self._load_sidecar():
+            self._rebuild_from_sqlite()
         print(f"✅ RAG Vector Store initialized: {storage_path}")
 
     # -- storage (same table as the reference, :270-296) ------------------------------------ #
@@ -171,6 +173,83 @@ class B200VectorStore:
             batch.append((doc_id, emb, ts, source))
         if batch:
             self._append_rows(batch)
+
+    # -- packed on-disk sidecar ----------------------------------------- #
+    # The reference persists vectors only as pickled Python lists inside SQLite (3 472 B per 384-d vector,
+    # ~20 us to unpickle, :358 / :487) and its FAISS index is volatile (:298-305).  On close the device rows go
+    # to disk exactly as they sit in HBM (fp16/bf16 rows + fp32 norms + the row table); on open they come back
+    # with one copy — if the table has not changed since (fingerprint), else the table wins and is re-read.
+    def _fingerprint(self) -> List[float]:
+        with sqlite3.connect(self.db_path) as conn:
+            row = conn.execute("SELECT COUNT(*), COALESCE(MAX(rowid), 0), COALESCE(SUM(timestamp), 0.0), "
+                               "COALESCE(SUM(LENGTH(embedding)), 0) FROM documents").fetchone()
+        return [float(x) for x in row]
+
+    def _sidecar_paths(self):
+        return (self.storage_path / "b200_rows.npy", self.storage_path / "b200_norms.npy", self.storage_path / "b200_meta.npz")
+
+    def save_sidecar(self) -> bool:
+        """Write the packed device rows + row table next to the SQLite file; returns False (and prints) on failure."""
+        try:
+            with self._lock:
+                if self._store is None or self._n == 0 or getattr(self, "_dim_is_placeholder", False):
+                    return False
+                n = self._n
+                rows, norms = self._store.get_rows(0, n)
+                p_rows, p_norms, p_meta = self._sidecar_paths()
+                np.save(p_rows, rows)
+                np.save(p_norms, norms)
+                names = [None] * len(self._src_code)
+                for name, code in self._src_code.items():
+                    names[code] = name
+                np.savez(p_meta, ids=np.array([self.document_mapping[r] for r in range(n)], dtype=np.str_),
+                         ts=self._ts[:n], src=self._src[:n], live=self._live[:n], has=self._has[:n],
+                         src_names=np.array(names, dtype=np.str_), dtype=np.array(self.dtype), dim=np.array(self._store.dim),
+                         monotone=np.array(self._monotone), fingerprint=np.array(self._fingerprint()))
+            return True
+        except Exception as e:
+            print(f"Sidecar save error: {e}")
+            return False
+
+    def _load_sidecar(self) -> bool:
+        p_rows, p_norms, p_meta = self._sidecar_paths()
+        if not (p_rows.exists() and p_norms.exists() and p_meta.exists()):
+            return False
+        try:
+            meta = np.load(p_meta, allow_pickle=False)
+            if str(meta["dtype"]) != self.dtype or not np.array_equal(meta["fingerprint"], np.array(self._fingerprint())):
+                return False  # another dtype was asked for, or the table changed behind the sidecar: re-read the table
+            rows = np.load(p_rows, mmap_mode="r")
+            norms = np.load(p_norms)
+            n, dim = rows.shape
+            if n != len(meta["ids"]) or n != len(norms) or dim != int(meta["dim"]):
+                return False
+            with self._lock:
+                self._store = DeviceStore(dim, self.dtype, max(self._capacity0, n), self.device)
+                for r0 in range(0, n, 262144):  # slabs: the memory-mapped file never sits in RAM as a whole
+                    r1 = min(n, r0 + 262144)
+                    self._store.put_rows(np.ascontiguousarray(rows[r0:r1]), norms[r0:r1])
+                self._grow_meta(n)
+                self._ts[:n], self._src[:n] = meta["ts"], meta["src"]
+                self._live[:n], self._has[:n] = meta["live"], meta["has"]
+                self._src_code = {str(name): i for i, name in enumerate(meta["src_names"].tolist())}
+                ids = meta["ids"].tolist()
+                self.document_mapping = dict(enumerate(ids))
+                self._row_of = {d: r for r, d in enumerate(ids) if self._live[r]}
+                self._monotone = bool(meta["monotone"])
+                self._n = n
+                self._meta_version += 1
+                self._push_meta(0, n, [])
+            self.restored_from = "sidecar"
+            return True
+        except Exception as e:
+            print(f"Sidecar load error (rebuilding from the table): {e}")
+            with self._lock:
+                if self._store is not None:
+                    self._store.close()
+                self._store, self._n = None, 0
+                self.document_mapping, self._row_of, self._src_code = {}, {}, {}
+            return False
 
     # -- host-side row table ------------------------------------------------------------------ #
     def _grow_meta(self, need: int):
@@ -472,9 +551,12 @@ class B200VectorStore:
             print(f"Stats error: {e}")
         return stats
 
-    def close(self) -> None:
+    def close(self, save: bool = True) -> None:
+        """Release the device store; by default the packed rows are written to the sidecar first."""
         with self._lock:
             if self._store is not None:
+                if save:
+                    self.save_sidecar()
                 self._store.close()
                 self._store = None
 

@@ -176,6 +176,17 @@ class DeviceStore:
         check(self._lib.ragb_store_get_rows(self._h, int(row0), int(n), rows.ctypes.data, norms.ctypes.data))
         return rows, norms
 
+    def put_rows(self, rows: np.ndarray, norms: np.ndarray) -> int:
+        """Append rows that are already packed (the arrays ``get_rows`` returned), verbatim; returns the first row."""
+        rows = np.ascontiguousarray(rows, dtype=_np_elem(self.dtype_code))
+        norms = np.ascontiguousarray(norms, dtype=np.float32)
+        if rows.ndim != 2 or rows.shape[1] != self.dim or norms.shape[0] != rows.shape[0]:
+            raise ValueError("expected packed rows [n, dim] and norms [n]")
+        self._room(rows.shape[0])
+        first = C.c_int64(-1)
+        check(self._lib.ragb_store_put_rows(self._h, rows.ctypes.data, norms.ctypes.data, rows.shape[0], C.byref(first)))
+        return first.value
+
     # -- search ----------------------------------------------------------------- #
     def search(self, q: np.ndarray, k: int, metric: str = "ip", threshold: float = NEG_INF, clamp01: bool = False,
                row_begin: int = 0, row_end: int = -1, valid: Optional[np.ndarray] = None,

@@ -204,3 +204,41 @@ def test_search_many_equals_looped_search(tmp_path):
         if not qy.source_filters:
             assert m.documents[0].id == f"d{(int(qy.query_text[1:]) * 37) % n}"
     assert many[-1].documents == [] and many[-1].similarities == []
+
+
+def test_sidecar_restores_bit_exact_and_yields_to_the_table(tmp_path):
+    """close() writes the packed rows; a new store on the same directory restores them with one copy (bit-equal
+    rows, same results); if the SQLite table changed behind the sidecar, the table is re-read instead."""
+    import sqlite3, pickle, json
+    from modular_rag_system_b200 import B200VectorStore, RAGDocument, RAGQuery
+    rng = np.random.default_rng(21)
+    n, d = 700, 128
+    X = rng.standard_normal((n, d))
+    vs = B200VectorStore(tmp_path / "sc", window=None)
+    docs = [RAGDocument(id=f"d{i}", content=f"doc {i}", metadata={"i": i}, embedding=X[i].tolist() if i % 50 else None,
+                        timestamp=10.0 + i, source=("a", "b")[i % 2]) for i in range(n)]
+    vs.embedding_generator.embedding_cache.update({f"doc {i}": None for i in range(n)})
+    vs.embedding_generator = type("E", (), {"embedding_cache": {}, "generate_embedding": lambda self, t: self.embedding_cache.get(t)})()
+    assert all(vs.add_documents(docs))
+    assert vs.add_document(RAGDocument(id="d7", content="doc 7 again", metadata={}, embedding=X[8].tolist(), timestamp=5000.0, source="a"))
+    vs.embedding_generator.embedding_cache["Q"] = X[8].tolist()
+    q = RAGQuery(query_text="Q", context={}, max_results=5, similarity_threshold=0.0, source_filters=["a"])
+    before = vs.search(q)
+    rows0, norms0 = vs._store.get_rows()
+    vs.close()
+    vs2 = B200VectorStore(tmp_path / "sc", window=None, embedding_generator=vs.embedding_generator)
+    assert vs2.restored_from == "sidecar"
+    rows1, norms1 = vs2._store.get_rows()
+    assert np.array_equal(rows0.view(np.uint16), rows1.view(np.uint16)) and np.array_equal(norms0, norms1)
+    after = vs2.search(q)
+    assert [x.id for x in after.documents] == [x.id for x in before.documents] and after.similarities == before.similarities
+    assert after.documents[0].id == "d7" and after.total_documents_searched == before.total_documents_searched
+    vs2.close()
+    with sqlite3.connect(tmp_path / "sc" / "rag_documents.db") as conn:  # somebody else (the reference) adds a row
+        conn.execute("INSERT INTO documents VALUES (?,?,?,?,?,?,?,?)",
+                     ("new", "new doc", json.dumps({}), pickle.dumps((X[8] * 3).tolist()), 9000.0, "a", 1.0, 0))
+    vs3 = B200VectorStore(tmp_path / "sc", window=None, embedding_generator=vs.embedding_generator)
+    assert vs3.restored_from == "sqlite"
+    res = vs3.search(q)
+    assert res.documents[0].id == "new" and res.documents[1].id == "d7"  # equal cosine 1.0: newer first
+    vs3.close(save=False)
