@@ -106,9 +106,25 @@ def cpu_sample(n_total: int, d: int, batch: int, k: int, target_s: float):
     return qps, t, n_s, cores
 
 
+def literal_rows_per_s(d: int, k: int, n_rows: int = 3000) -> float:
+    """The reference's algorithm as written — one Python-level cosine per stored row (ollama_rag_system.py:480-508,
+    :199-222), lists in, float64 inside — on `n_rows` rows, one query, one core (it holds the GIL)."""
+    import numpy as np
+    from oracle import ref_search
+    rng = np.random.default_rng(3)
+    rows = [(i, rng.standard_normal(d).tolist()) for i in range(n_rows)]
+    q = rng.standard_normal(d).tolist()
+    t0 = time.perf_counter()
+    ref_search.search_literal(rows, q, k, 0.0)
+    return n_rows / (time.perf_counter() - t0)
+
+
 def cpu_baseline_obj(wl, batch, k, target_s):
     qps, t, n_s, cores = cpu_sample(wl["n"], wl["d"], batch, k, target_s)
+    lit = literal_rows_per_s(wl["d"], k)
     return {
+        "literal_loop": {"rows_per_s": lit, "queries_per_s_extrapolated": lit / wl["n"], "cores": 1,
+                         "what": "oracle.search_literal = the reference's per-row Python loop, 3000 rows x 1 query, scaled linearly"},
         "value": qps, "unit": "queries/s", "cores": cores, "kind": "port",
         "sample": (f"oracle.search_f64_blocked (numpy float64 GEMM + top-k, all BLAS threads) on {n_s} of "
                    f"{wl['n']} rows x {wl['d']}, batch {batch}: {t:.2f} s; scaled linearly in rows"),

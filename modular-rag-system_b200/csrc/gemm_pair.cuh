@@ -83,7 +83,10 @@ template <int E> struct CandCfg {
   static constexpr int cap = E == 2 ? kPairCapSmall : 32 * E;
   static constexpr int stride = E == 2 ? kPairCapSmall + 1 : 32 * E;  // +1: conflict-free for both access patterns
 };
-constexpr int kChunkRows = 32;  // rows behind one candidate key (one tcgen05.ld of 32 columns)
+// rows behind one candidate key.  k <= 32 (E == 2): 16 — half of one tcgen05.ld of 32 columns; the finish kernel then
+// re-reads half as many rows (1M x 384, B=1024: 133 -> 96 us).  k > 32: 32 — twice the chunks would double the
+// inserts into the global-memory buffers, which costs more than the finish kernel saves (1M x 384 top-100: +8 %).
+template <int E> struct ChunkCfg { static constexpr int rows = E == 2 ? 16 : 32; };
 
 __device__ __forceinline__ float fmax3(float a, float b, float c) {
   float r;
@@ -163,14 +166,14 @@ __device__ __forceinline__ uint64_t warp_prune(uint64_t* base, int n, int k, int
 }
 
 // ---- the fused top-k epilogue: CHUNK-granular selection -----------------------------------------
-// Thread == query holds the scores of its query against 32 consecutive rows (one chunk).  The epilogue
-// keeps, per query, the best k_sel CHUNKS ranked by (chunk maximum, chunk start row): a 3-input max
-// tree and one compare per chunk, and — rarely, about k*ln(chunks/k) times per query — one store.
+// Thread == query holds the scores of its query against 32 consecutive rows (two chunks of 16).  The epilogue
+// keeps, per query, the best k_sel CHUNKS (16 consecutive rows) ranked by (chunk maximum, chunk start
+// row): a 3-input max tree and one compare per chunk, and — rarely, about k*ln(chunks/k) times per query — one store.
 // Why that is exact: the k best rows of a query lie inside its k best chunks.  (A chunk outside them
 // is beaten by k chunks whose maximum rows each beat every row of it — by score, or on equal score by
 // the larger row id, since a later chunk holds later rows.)  The k-th best chunk maximum is therefore
 // also a valid running threshold.  rescore_chunks_kernel then scores the 32 rows of every selected
-// chunk in fp32 and the merge keeps the k best rows; row range, valid mask and the user threshold are
+// chunk in fp32 and keeps the k best rows; row range, valid mask and the user threshold are
 // applied there, exactly.  Here rows outside the range / masked out are only kept from raising a
 // chunk's maximum (kMasked), so the threshold stays a lower bound.
 struct EpiCtx {
@@ -179,35 +182,45 @@ struct EpiCtx {
   int cnt;
   float user_fast, fthr;
 };
-template <bool kMasked>
+// max of 16 consecutive columns: five 3-input maxima, then 6 -> 2 -> 1
+__device__ __forceinline__ float max16(const uint32_t* r) {
+  float t[5];
+#pragma unroll
+  for (int i = 0; i < 5; ++i)
+    t[i] = fmax3(__uint_as_float(r[3 * i]), __uint_as_float(r[3 * i + 1]), __uint_as_float(r[3 * i + 2]));
+  return fmaxf(fmax3(t[0], t[1], t[2]), fmax3(t[3], t[4], __uint_as_float(r[15])));
+}
+// one tcgen05.ld of 32 columns = two chunks of 16 rows (kRows == 16) or one chunk of 32
+template <bool kMasked, int kRows>
 __device__ __forceinline__ void epi_chunk(EpiCtx& e, uint32_t (&r)[32], int64_t row_c, const TsParams& p, int lane) {
-  bool any_row = true;
+  bool any_a = true, any_b = true;
   if (kMasked) {
     const int64_t row = row_c + lane;
     bool v = row < p.row_end;
     if (v && p.valid) v = p.valid[row] != 0;
     const unsigned vb = __ballot_sync(0xffffffffu, v);
-    any_row = vb != 0;
+    any_a = (vb & 0xffffu) != 0;
+    any_b = (vb >> 16) != 0;
     if (vb != 0xffffffffu) {
 #pragma unroll
       for (int j = 0; j < 32; ++j)
         if (!((vb >> j) & 1u)) r[j] = 0xff800000u;  // -inf: cannot raise the chunk maximum
     }
   }
-  float t[11];
-#pragma unroll
-  for (int i = 0; i < 10; ++i)
-    t[i] = fmax3(__uint_as_float(r[3 * i]), __uint_as_float(r[3 * i + 1]), __uint_as_float(r[3 * i + 2]));
-  t[10] = fmaxf(__uint_as_float(r[30]), __uint_as_float(r[31]));
-  const float u0 = fmax3(t[0], t[1], t[2]), u1 = fmax3(t[3], t[4], t[5]), u2 = fmax3(t[6], t[7], t[8]);
-  const float mx = fmax3(fmax3(u0, u1, u2), t[9], t[10]);
-  if (mx >= e.fthr && any_row) e.my[e.cnt++] = make_key(finish_score(mx, 1.0f, p.flags), (uint32_t)row_c);
+  const float ma = max16(&r[0]), mb = max16(&r[16]);
+  if constexpr (kRows == 16) {
+    if (ma >= e.fthr && any_a) e.my[e.cnt++] = make_key(finish_score(ma, 1.0f, p.flags), (uint32_t)row_c);
+    if (mb >= e.fthr && any_b) e.my[e.cnt++] = make_key(finish_score(mb, 1.0f, p.flags), (uint32_t)row_c + 16);
+  } else {
+    const float mx = fmaxf(ma, mb);
+    if (mx >= e.fthr && (any_a || any_b)) e.my[e.cnt++] = make_key(finish_score(mx, 1.0f, p.flags), (uint32_t)row_c);
+  }
 }
-// once per tile (a query gains at most 8 chunks per tile): prune the buffers that could overflow next tile
+// once per tile (a query gains at most kPairN / rows-per-chunk = 16 or 8 chunks per tile): prune the buffers that could overflow next tile
 template <int E>
 __device__ __forceinline__ void epi_prune(EpiCtx& e, const TsParams& p, int lane) {
   constexpr int kCap = CandCfg<E>::cap, kStride = CandCfg<E>::stride;
-  unsigned need = __ballot_sync(0xffffffffu, e.cnt > kCap - kPairN / kChunkRows);
+  unsigned need = __ballot_sync(0xffffffffu, e.cnt > kCap - kPairN / ChunkCfg<E>::rows);
   while (need) {
     const int j = __ffs(need) - 1;
     need &= need - 1;
@@ -359,20 +372,20 @@ gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_co
         for (int c = 0; c < kPairN / 32; c += 2) {
           tc_wait_ld_dep(ra);
           tc_ld32(taddr + (c + 1) * 32, rb);
-          epi_chunk<false>(e, ra, row0 + c * 32, p, lane);
+          epi_chunk<false, ChunkCfg<E>::rows>(e, ra, row0 + c * 32, p, lane);
           tc_wait_ld_dep(rb);
           if (c + 2 < kPairN / 32) tc_ld32(taddr + (c + 2) * 32, ra);
-          epi_chunk<false>(e, rb, row0 + (c + 1) * 32, p, lane);
+          epi_chunk<false, ChunkCfg<E>::rows>(e, rb, row0 + (c + 1) * 32, p, lane);
         }
       } else {  // valid mask given, or the tile reaches past row_end
 #pragma unroll 1
         for (int c = 0; c < kPairN / 32; c += 2) {
           tc_wait_ld_dep(ra);
           tc_ld32(taddr + (c + 1) * 32, rb);
-          epi_chunk<true>(e, ra, row0 + c * 32, p, lane);
+          epi_chunk<true, ChunkCfg<E>::rows>(e, ra, row0 + c * 32, p, lane);
           tc_wait_ld_dep(rb);
           if (c + 2 < kPairN / 32) tc_ld32(taddr + (c + 2) * 32, ra);
-          epi_chunk<true>(e, rb, row0 + (c + 1) * 32, p, lane);
+          epi_chunk<true, ChunkCfg<E>::rows>(e, rb, row0 + (c + 1) * 32, p, lane);
         }
       }
       tc_fence_before();

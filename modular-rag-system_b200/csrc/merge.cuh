@@ -72,8 +72,8 @@ __global__ void __launch_bounds__(kMergeThreads) merge_topk_kernel(const MergePa
 // ---------------------------------------------------------------------------------------------
 // K5' finish of the SM-pair batched kernel (gemm_pair.cuh), ONE launch, one CTA per query:
 //   1. fold the per-split lists of CHUNK keys (score = chunk maximum from the 16-bit-query tensor pass,
-//      id = local start row of the 32-row chunk) into the best k_sel chunks;
-//   2. score the 32 rows of each selected chunk exactly: fp32 query, fp32 accumulate, 8 lanes per row
+//      id = local start row of the 16-row chunk) into the best k_sel chunks;
+//   2. score the 16 rows of each selected chunk exactly: fp32 query, fp32 accumulate, 8 lanes per row
 //      reading consecutive 16-byte pieces (a warp instruction touches 4 cache lines, not 32), and apply
 //      what the reference applies per row (ollama_rag_system.py:480-508): row window, valid mask, clamp,
 //      `>= threshold`;
@@ -95,7 +95,7 @@ struct FinishParams {
   uint64_t* out_keys;     // [nq][kpad] or null
   PeerOut peers;          // peers.n > 0: the kpad sorted keys also go to every rank's gather buffer
 };
-constexpr int kFinishChunkRows = 32;
+constexpr int kFinishMaxChunkRows = 32;
 
 // number of keys of a descending-sorted list (zeros at the tail) that are greater than `key`
 __device__ __forceinline__ int count_greater_sorted(const uint64_t* list, int len_pow2, uint64_t key) {
@@ -107,11 +107,16 @@ __device__ __forceinline__ int count_greater_sorted(const uint64_t* list, int le
 
 // shared memory: lists [n_lists*kpad] | chunk [kpad] | cmax [kpad] | surv [kpad*32] | final [kpad] | misc
 __host__ __device__ inline size_t finish_smem_bytes(int n_lists, int kpad) {
-  return ((size_t)n_lists * kpad + (size_t)kpad * (3 + kFinishChunkRows)) * sizeof(uint64_t) + 16;
+  return ((size_t)n_lists * kpad + (size_t)kpad * (3 + kFinishMaxChunkRows)) * sizeof(uint64_t) + 16;
 }
 
-template <typename T>
+// kRows = rows per chunk: 16 (a half-warp per chunk, two chunks per warp at a time) or 32 (a warp per chunk)
+template <typename T, int kRows>
 __global__ void __launch_bounds__(kMergeThreads, 3) finish_chunks_kernel(const FinishParams p) {
+  constexpr int kFinishChunkRows = kRows;
+  constexpr int kPerWarp = 32 / kRows;            // chunks a warp scores at a time
+  constexpr int kLaneMask = kRows - 1;            // lane -> row of its chunk
+  constexpr int kGroups = kRows / 8;              // 8-lane groups per chunk: 2 or 4
   extern __shared__ __align__(16) uint64_t fsm[];
   constexpr int E = Elem<T>::per16;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -120,7 +125,7 @@ __global__ void __launch_bounds__(kMergeThreads, 3) finish_chunks_kernel(const F
   uint64_t* chunk = lists + (size_t)p.n_lists * p.kpad;  // selected chunk keys, by rank
   uint64_t* cmax = chunk + p.kpad;                        // exact key of the best row of each selected chunk
   uint64_t* surv = cmax + p.kpad;                         // rows that can still be among the k best
-  uint64_t* fin = surv + (size_t)p.kpad * kFinishChunkRows;
+  uint64_t* fin = surv + (size_t)p.kpad * kFinishMaxChunkRows;
   int* misc = reinterpret_cast<int*>(fin + p.kpad);       // [0] survivor count  [1..2] threshold key
 
   // ---- 1. best k_sel chunks: rank every key by counting (lists are sorted, keys are unique) ----
@@ -148,19 +153,22 @@ __global__ void __launch_bounds__(kMergeThreads, 3) finish_chunks_kernel(const F
   __syncthreads();
 
   // ---- 2. exact scores of the rows of the selected chunks (registers: my_key of row start+lane) ----
-  const int g = lane >> 3, l = lane & 7;  // lane group g scores rows start + 4r + g, r = 0..7; 8 lanes per row
+  // kRows lanes per chunk, 8 lanes per row: lane group gq of the chunk scores rows start + kGroups*r + gq, r = 0..7
+  const int hw = lane / kRows, gq = (lane >> 3) & (kGroups - 1), l = lane & 7;
   const int pieces = (int)(p.ld / E);     // ld is padded to 16 bytes, padding columns are zero
   const bool q_vec = (p.dim % 4 == 0) && ((reinterpret_cast<uintptr_t>(qv) & 15) == 0);
-  for (int c = warp; c < p.k_sel; c += kMergeWarps) {
-    const uint64_t ckey = chunk[c];
-    if (ckey == 0) continue;  // warp-uniform
+  for (int c0 = kPerWarp * warp; c0 < p.k_sel; c0 += kPerWarp * kMergeWarps) {
+    const int c = c0 + hw;
+    const uint64_t ckey = c < p.k_sel ? chunk[c] : 0ull;
+    const bool active = ckey != 0;
+    if (!__any_sync(0xffffffffu, active)) continue;
     const int64_t start = (int64_t)key_id(ckey);
     // per 16-byte piece of the query, eight independent row loads are in flight and the query piece is
     // loaded once for all eight rows
     float acc[8];
 #pragma unroll
     for (int r = 0; r < 8; ++r) acc[r] = 0.f;
-    const T* x0 = static_cast<const T*>(p.X) + (size_t)(start + g) * p.ld;
+    const T* x0 = static_cast<const T*>(p.X) + (size_t)(start + gq) * p.ld;
 #pragma unroll 1
     for (int pc = l; pc < pieces; pc += 8) {
       float qf[E];
@@ -178,8 +186,8 @@ __global__ void __launch_bounds__(kMergeThreads, 3) finish_chunks_kernel(const F
       uint4 v[8];
 #pragma unroll
       for (int r = 0; r < 8; ++r)
-        v[r] = (start + 4 * r + g < p.row_end)
-                   ? ld_stream16(reinterpret_cast<const uint4*>(x0 + (size_t)(4 * r) * p.ld) + pc)
+        v[r] = (active && start + kGroups * r + gq < p.row_end)
+                   ? ld_stream16(reinterpret_cast<const uint4*>(x0 + (size_t)(kGroups * r) * p.ld) + pc)
                    : make_uint4(0, 0, 0, 0);
 #pragma unroll
       for (int r = 0; r < 8; ++r) {
@@ -198,23 +206,24 @@ __global__ void __launch_bounds__(kMergeThreads, 3) finish_chunks_kernel(const F
       a += __shfl_xor_sync(0xffffffffu, a, 4);
       a += __shfl_xor_sync(0xffffffffu, a, 2);
       a += __shfl_xor_sync(0xffffffffu, a, 1);
-      // lane L keeps the score of row start+L = start + 4*(L/4) + L%4: held by the 8 lanes of group L%4
-      const float v2 = __shfl_sync(0xffffffffu, a, (lane & 3) * 8);
-      if ((lane >> 2) == r) mine = v2;
+      // lane j of the chunk keeps the score of row start+j = start + kGroups*(j/kGroups) + j%kGroups: held by lane
+      // group j%kGroups of the chunk's lanes
+      const float v2 = __shfl_sync(0xffffffffu, a, (lane & ~kLaneMask) + (lane & (kGroups - 1)) * 8);
+      if (((lane & kLaneMask) / kGroups) == r) mine = v2;
     }
-    const int64_t row = start + lane;
+    const int64_t row = start + (lane & kLaneMask);
     const float sc = finish_score(mine, scale, p.flags);
-    bool ok = row >= p.row_begin && row < p.row_end && sc >= p.threshold;
+    bool ok = active && row >= p.row_begin && row < p.row_end && sc >= p.threshold;
     if (ok && p.valid) ok = p.valid[row] != 0;
     const uint64_t key = ok ? make_key(sc, (uint32_t)row + p.id_base) : 0ull;
-    surv[c * kFinishChunkRows + lane] = key;  // parked; filtered below
+    if (active) surv[c * kFinishChunkRows + (lane & kLaneMask)] = key;  // parked; filtered below
     uint64_t m = key;
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
+    for (int o = kRows / 2; o > 0; o >>= 1) {
       const uint64_t t = __shfl_xor_sync(0xffffffffu, m, o);
       m = t > m ? t : m;
     }
-    if (lane == 0) cmax[c] = m;
+    if ((lane & kLaneMask) == 0 && active) cmax[c] = m;
   }
   __syncthreads();
 
@@ -231,7 +240,7 @@ __global__ void __launch_bounds__(kMergeThreads, 3) finish_chunks_kernel(const F
   __syncthreads();
   const uint64_t tau = ((uint64_t)(uint32_t)misc[2] << 32) | (uint32_t)misc[1];  // 0 when fewer than k chunks hold a row
   // compact the survivors in place: slot order does not matter, ranks are computed against the whole set
-  uint64_t mykeys[(128 * kFinishChunkRows) / kMergeThreads];
+  uint64_t mykeys[(128 * kFinishChunkRows) / kMergeThreads];  // k_sel <= 128 chunks
   int n_mine = 0;
   const int n_cand = p.k_sel * kFinishChunkRows;
 #pragma unroll

@@ -672,7 +672,6 @@ static int gemm_finish_chunks(ragb_store* s, const float* q, int64_t nq, int k, 
                               float threshold, int flags, int64_t rb, int64_t re, const uint8_t* valid, uint32_t id_base,
                               const uint64_t* parts, int splits, uint64_t* out_keys, float* out_scores, int64_t* out_ids,
                               cudaStream_t st) {
-  static_assert(kFinishChunkRows == kChunkRows, "epilogue and finish kernel disagree on the chunk size");
   FinishParams f = {};
   f.parts = parts; f.n_lists = splits; f.kpad = kpad; f.k_sel = k_sel; f.k = k;
   f.X = s->rows; f.ld = s->ld; f.dim = s->dim; f.q = q; f.metric = metric; f.flags = flags; f.threshold = threshold;
@@ -681,13 +680,14 @@ static int gemm_finish_chunks(ragb_store* s, const float* q, int64_t nq, int k, 
   f.peers = s->peer;
   const size_t smem = finish_smem_bytes(splits, kpad);
   if (smem > 200 * 1024) return fail(RAGB_EUNSUPPORTED, "internal: %d splits x kpad %d do not fit the finish kernel", splits, kpad);
-  if (s->dtype == RAGB_BF16) {
-    if (smem > 48 * 1024) CU_TRY(cudaFuncSetAttribute(finish_chunks_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    finish_chunks_kernel<__nv_bfloat16><<<(unsigned)nq, kMergeThreads, smem, st>>>(f);
-  } else {
-    if (smem > 48 * 1024) CU_TRY(cudaFuncSetAttribute(finish_chunks_kernel<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    finish_chunks_kernel<__half><<<(unsigned)nq, kMergeThreads, smem, st>>>(f);
-  }
+  // rows per chunk must match the epilogue that produced the keys (gemm_pair.cuh: ChunkCfg)
+  typedef void (*FinishKernel)(const FinishParams);
+  const bool small = kpad <= 32;
+  static_assert(ChunkCfg<2>::rows == 16 && ChunkCfg<4>::rows == 32 && ChunkCfg<8>::rows == 32, "finish kernel variants");
+  FinishKernel kern = s->dtype == RAGB_BF16 ? (small ? finish_chunks_kernel<__nv_bfloat16, 16> : finish_chunks_kernel<__nv_bfloat16, 32>)
+                                            : (small ? finish_chunks_kernel<__half, 16> : finish_chunks_kernel<__half, 32>);
+  if (smem > 48 * 1024) CU_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  kern<<<(unsigned)nq, kMergeThreads, smem, st>>>(f);
   LAUNCHED();
   return RAGB_OK;
 }

@@ -76,31 +76,81 @@ __device__ __forceinline__ void fused_final_merge(WarpTopK& tk, uint64_t* smem_l
   __syncthreads();
   if (!is_last) return;
   __threadfence();
-  tk.init(smem_lists + (size_t)warp * listbuf_len(p.kpad), p.k, p.kpad, lane);
   const uint64_t* base = p.out + (size_t)blockIdx.y * gridDim.x * p.kpad;
-  const int total = (int)gridDim.x * p.kpad;
-  for (int i0 = warp * 32; i0 < total; i0 += kScanWarps * 32) {
-    const uint64_t key = (i0 + lane < total) ? __ldcg(base + i0 + lane) : 0ull;
-    tk.push(key > tk.thr, key, lane);
-  }
-  tk.flush(lane);
-  __syncthreads();
-  for (int s = 1; s < kScanWarps; s <<= 1) {
-    if ((warp & (2 * s - 1)) == 0 && warp + s < kScanWarps)
-      tk.merge_list(smem_lists + (size_t)(warp + s) * tk.len, lane);
+  const int P = (int)gridDim.x;
+  const int64_t qi = blockIdx.y;
+  const int smem_keys = kScanWarps * listbuf_len(p.kpad);
+  if (P + (p.k + 1) * p.kpad <= smem_keys) {
+    // Rank counting instead of merge networks.  Every list is sorted, so the k-th largest list HEAD bounds the
+    // k-th best key from below (k distinct rows reach it): only the <= k lists whose head reaches it can hold a
+    // winner, i.e. at most k*kpad survivors, each ranked by counting the survivors above it.
+    uint64_t* heads = smem_lists;
+    uint64_t* fin = heads + P;
+    uint64_t* surv = fin + p.kpad;
+    __shared__ unsigned long long tau_s;
+    __shared__ int n_surv_s;
+    for (int i = threadIdx.x; i < P; i += kScanThreads) heads[i] = __ldcg(base + (size_t)i * p.kpad);
+    for (int i = threadIdx.x; i < p.kpad; i += kScanThreads) fin[i] = 0;
+    if (threadIdx.x == 0) { tau_s = 0ull; n_surv_s = 0; }
     __syncthreads();
-  }
-  if (warp == 0) {
-    const int64_t qi = blockIdx.y;
-    for (int i = lane; i < p.k; i += 32) {
-      const uint64_t key = tk.buf[i];
-      if (p.out_scores) p.out_scores[qi * p.k + i] = key ? key_score(key) : -INFINITY;
-      if (p.out_ids) p.out_ids[qi * p.k + i] = key ? (int64_t)key_id(key) : -1;
+    for (int i = threadIdx.x; i < P; i += kScanThreads) {
+      const uint64_t h = heads[i];
+      if (h == 0) continue;
+      int rank = 0;
+      for (int j = 0; j < P; ++j) rank += heads[j] > h ? 1 : 0;
+      if (rank == p.k - 1) tau_s = h;
     }
-    if (p.out_keys)
-      for (int i = lane; i < p.kpad; i += 32) p.out_keys[qi * p.kpad + i] = i < p.k ? tk.buf[i] : 0;
-    if (p.peers.n)
-      for (int i = lane; i < p.kpad; i += 32) peer_emit(p.peers, qi * p.kpad + i, i < p.k ? tk.buf[i] : 0);
+    __syncthreads();
+    const uint64_t tau = tau_s;  // 0 when fewer than k lists hold anything: everything survives
+    for (int i = threadIdx.x; i < P * p.kpad; i += kScanThreads) {
+      const int l = i / p.kpad;
+      if (heads[l] == 0 || heads[l] < tau) continue;
+      const uint64_t key = __ldcg(base + i);
+      if (key != 0 && key >= tau) surv[atomicAdd(&n_surv_s, 1)] = key;
+    }
+    __syncthreads();
+    const int n_surv = n_surv_s;
+    for (int i = threadIdx.x; i < n_surv; i += kScanThreads) {
+      const uint64_t key = surv[i];
+      int rank = 0;
+      for (int j = 0; j < n_surv && rank < p.k; ++j) rank += surv[j] > key ? 1 : 0;
+      if (rank < p.k) fin[rank] = key;
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < p.kpad; i += kScanThreads) {
+      const uint64_t key = fin[i];
+      if (i < p.k) {
+        if (p.out_scores) p.out_scores[qi * p.k + i] = key ? key_score(key) : -INFINITY;
+        if (p.out_ids) p.out_ids[qi * p.k + i] = key ? (int64_t)key_id(key) : -1;
+      }
+      if (p.out_keys) p.out_keys[qi * p.kpad + i] = key;
+      if (p.peers.n) peer_emit(p.peers, qi * p.kpad + i, key);
+    }
+  } else {
+    tk.init(smem_lists + (size_t)warp * listbuf_len(p.kpad), p.k, p.kpad, lane);
+    const int total = P * p.kpad;
+    for (int i0 = warp * 32; i0 < total; i0 += kScanWarps * 32) {
+      const uint64_t key = (i0 + lane < total) ? __ldcg(base + i0 + lane) : 0ull;
+      tk.push(key > tk.thr, key, lane);
+    }
+    tk.flush(lane);
+    __syncthreads();
+    for (int s = 1; s < kScanWarps; s <<= 1) {
+      if ((warp & (2 * s - 1)) == 0 && warp + s < kScanWarps)
+        tk.merge_list(smem_lists + (size_t)(warp + s) * tk.len, lane);
+      __syncthreads();
+    }
+    if (warp == 0) {
+      for (int i = lane; i < p.k; i += 32) {
+        const uint64_t key = tk.buf[i];
+        if (p.out_scores) p.out_scores[qi * p.k + i] = key ? key_score(key) : -INFINITY;
+        if (p.out_ids) p.out_ids[qi * p.k + i] = key ? (int64_t)key_id(key) : -1;
+      }
+      if (p.out_keys)
+        for (int i = lane; i < p.kpad; i += 32) p.out_keys[qi * p.kpad + i] = i < p.k ? tk.buf[i] : 0;
+      if (p.peers.n)
+        for (int i = lane; i < p.kpad; i += 32) peer_emit(p.peers, qi * p.kpad + i, i < p.k ? tk.buf[i] : 0);
+    }
   }
   if (p.peers.n) peer_signal(p.peers, gridDim.y);  // one merging CTA per query
 }
