@@ -11,7 +11,8 @@
  *     ragb_last_error() gives a thread-local message.  Nothing throws.
  *   - "host" entry points take plain host pointers and copy; "_dev" entry
  *     points take device pointers on the store's GPU plus a cudaStream_t passed
- *     as void* (NULL = the store's own stream, synchronised before return).
+ *     as void* (NULL = the store's own stream, synchronised before return; to run on the legacy default stream
+ *     asynchronously pass cudaStreamLegacy, i.e. (void*)1).
  *   - result slots: k per query, best first; unused slots hold id -1 and
  *     score -inf.  Order: score descending, then larger row id first (the
  *     reference's stable sort over "ORDER BY timestamp DESC" rows,

@@ -11,7 +11,7 @@ import subprocess
 from pathlib import Path
 
 CSRC = Path(__file__).resolve().parent / "csrc"
-LIB_PATH = CSRC / "libragb200.so"
+LIB_PATH = Path(os.environ["RAGB200_LIB"]) if os.environ.get("RAGB200_LIB") else CSRC / "libragb200.so"  # override: A/B runs of build variants
 
 F16, BF16, F32 = 0, 1, 2
 MASK_U8, MASK_I32, MASK_I64, MASK_F32 = 0, 1, 2, 3

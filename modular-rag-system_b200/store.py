@@ -53,8 +53,13 @@ def _torch_mask_code(t) -> int:
 
 
 def _cur_stream(device_index: int) -> int:
+    """Handle of torch's current stream for the C ABI.  The ABI reads NULL as "no stream given: use the store's own
+    stream and synchronise before returning"; torch's default stream IS handle 0, so it is passed as
+    cudaStreamLegacy (0x1) — the same stream by its explicit name — and the call stays asynchronous and ordered
+    with the torch work around it."""
     import torch
-    return torch.cuda.current_stream(device_index).cuda_stream
+    h = torch.cuda.current_stream(device_index).cuda_stream
+    return h if h else 1
 
 
 class DeviceStore:
