@@ -141,3 +141,28 @@ def test_pooled_rows_are_searchable():
     q = tok[17].float().mean(0).cpu().numpy()
     ids, sc = s.search(q, 1, "cosine")
     assert ids[0][0] == 17 and sc[0][0] > 0.999
+
+
+def test_pool_full_size_slab_properties():
+    """BASELINE configs[2] shape (seq 256, hidden 384, fp16 tokens, ragged u8 masks), one 16 384-chunk slab of the
+    1M: every packed row is a unit vector, the stored norm is the norm of the masked mean, and the result equals a
+    torch fp32 statement of Pooling(mean) + Normalize on the same device tensors."""
+    import torch
+    from modular_rag_system_b200 import DeviceStore
+    B, S, H = 16384, 256, 384
+    g = torch.Generator(device="cuda").manual_seed(2)
+    tok = torch.randn((B, S, H), generator=g, device="cuda", dtype=torch.float16)
+    lens = torch.randint(16, S + 1, (B, 1), generator=g, device="cuda")
+    mask = (torch.arange(S, device="cuda")[None, :] < lens).to(torch.uint8).contiguous()
+    st = DeviceStore(H, "fp16", B)
+    st.add_pooled_dev(tok, mask)
+    torch.cuda.synchronize()
+    rows, norms = st.get_rows(0, B)
+    m = mask.float()
+    mean = (tok.float() * m[:, :, None]).sum(1) / m.sum(1, keepdim=True).clamp(min=1e-9)
+    ref = torch.nn.functional.normalize(mean, p=2, dim=1, eps=1e-12)
+    got = torch.from_numpy(rows.astype(np.float32)).cuda()
+    assert (got - ref).abs().max().item() < 1e-3                      # one fp16 rounding of a unit vector's entry
+    assert (got.norm(dim=1) - 1).abs().max().item() < 2e-3
+    assert np.allclose(norms, mean.norm(dim=1).cpu().numpy(), rtol=1e-4)
+    st.close()
