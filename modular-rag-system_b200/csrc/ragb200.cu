@@ -71,6 +71,9 @@ struct ragb_store {
   void* rows = nullptr;
   float* norms = nullptr;
   cudaStream_t stream = nullptr;
+  cudaEvent_t ingest_ev = nullptr;  // last ingest launched on a caller's stream; the store's own stream waits on it
+  cudaEvent_t search_ev = nullptr;  // last search launched on a caller's stream (it uses ws / tickets): same
+  bool search_ev_used = false;
   std::mutex add_mu, search_mu;
   // search workspace (guarded by search_mu)
   void* ws = nullptr;
@@ -185,6 +188,8 @@ extern "C" int ragb_store_create(int device, int dim, int dtype, int64_t capacit
   if (r != RAGB_OK) { delete s; return r; }
   e = cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking);
   if (e != cudaSuccess) { cudaFree(s->rows); cudaFree(s->norms); delete s; return fail(RAGB_ECUDA, "cudaStreamCreate: %s", cudaGetErrorString(e)); }
+  cudaEventCreateWithFlags(&s->ingest_ev, cudaEventDisableTiming);
+  cudaEventCreateWithFlags(&s->search_ev, cudaEventDisableTiming);
   e = cudaMalloc(&s->tickets, (kScanMaxQ + 1) * sizeof(unsigned));
   if (e != cudaSuccess) { cudaStreamDestroy(s->stream); cudaFree(s->rows); cudaFree(s->norms); delete s; return fail(RAGB_ENOMEM, "cudaMalloc tickets: %s", cudaGetErrorString(e)); }
   cudaMemsetAsync(s->tickets, 0, (kScanMaxQ + 1) * sizeof(unsigned), s->stream);
@@ -206,6 +211,8 @@ extern "C" int ragb_store_destroy(ragb_store* s) {
     if (s->stage_host) cudaFreeHost(s->stage_host);
     if (s->pin) cudaFreeHost(s->pin);
     for (auto& ev : s->prof_events) { cudaEventDestroy(ev.first); cudaEventDestroy(ev.second); }
+    if (s->ingest_ev) cudaEventDestroy(s->ingest_ev);
+    if (s->search_ev) cudaEventDestroy(s->search_ev);
     cudaStreamDestroy(s->stream);
   }
   delete s;
@@ -383,9 +390,11 @@ extern "C" int ragb_store_add_dev(ragb_store* s, const void* rows, int in_dtype,
   RB_TRY(reserve_rows(s, n, &first));
   cudaStream_t st = stream ? (cudaStream_t)stream : s->stream;
   RB_TRY(norm_pack_any(rows, in_dtype, n, s->dim, ld_in, row_ptr(s, first), s->dtype, s->ld, s->norms + first, st));
-  // the new rows become searchable once the kernel is done (on a caller stream later
-  // searches are ordered behind it; our own stream is synchronised here)
+  // the new rows become searchable once the kernel is done: our own stream is synchronised here; on a caller's
+  // stream later work of that stream is ordered behind it, and the store's own stream (host entry points) is
+  // made to wait for it
   if (!stream) CU_TRY(cudaStreamSynchronize(st));
+  else if (s->ingest_ev) { CU_TRY(cudaEventRecord(s->ingest_ev, st)); CU_TRY(cudaStreamWaitEvent(s->stream, s->ingest_ev, 0)); }
   s->n.store(first + n, std::memory_order_release);
   if (out_first_row) *out_first_row = first;
   return RAGB_OK;
@@ -438,6 +447,7 @@ extern "C" int ragb_store_add_pooled_dev(ragb_store* s, const void* tok, int tok
   cudaStream_t st = stream ? (cudaStream_t)stream : s->stream;
   RB_TRY(pool_any(tok, tok_dtype, mask, mask_dtype, batch, seq, hidden, row_ptr(s, first), s->dtype, s->ld, s->norms + first, st));
   if (!stream) CU_TRY(cudaStreamSynchronize(st));
+  else if (s->ingest_ev) { CU_TRY(cudaEventRecord(s->ingest_ev, st)); CU_TRY(cudaStreamWaitEvent(s->stream, s->ingest_ev, 0)); }
   s->n.store(first + batch, std::memory_order_release);
   if (out_first_row) *out_first_row = first;
   return RAGB_OK;
@@ -989,6 +999,14 @@ static int check_search_args(ragb_store* s, const void* q, int64_t nq, int k, in
 }
 
 static int resolve_valid(ragb_store* s, const uint8_t** valid, int64_t row_end, bool* is_store_filter);
+// A search launched on a caller's stream uses the store's workspace; the store's own stream (host entry points)
+// must not start its next search before that one is done.  One caller stream at a time per store is the contract.
+static void mark_caller_search(ragb_store* s, cudaStream_t st) {
+  if (s->search_ev && cudaEventRecord(s->search_ev, st) == cudaSuccess) s->search_ev_used = true;
+}
+static void own_stream_waits(ragb_store* s) {
+  if (s->search_ev_used && cudaStreamWaitEvent(s->stream, s->search_ev, 0) == cudaSuccess) s->search_ev_used = false;
+}
 
 // core: device pointers, caller holds search_mu and has selected the device.
 // Writes sorted keys (out_keys, kpad per query) and/or decoded (out_scores, out_ids).
@@ -1044,10 +1062,12 @@ extern "C" int ragb_search_keys_dev(ragb_store* s, const float* q, int64_t nq, i
   std::lock_guard<std::mutex> ls(s->search_mu);
   ON_DEVICE(s->device);
   cudaStream_t st = stream ? (cudaStream_t)stream : s->stream;
+  if (!stream) own_stream_waits(s);
   bool sf;
   RB_TRY(resolve_valid(s, &valid, row_end, &sf));
   RB_TRY(search_core(s, q, nq, k, metric, threshold, flags, row_begin, row_end, valid, id_base, out_keys, nullptr, nullptr, st));
   if (!stream) CU_TRY(cudaStreamSynchronize(st));
+  else mark_caller_search(s, st);
   return RAGB_OK;
 }
 
@@ -1094,6 +1114,7 @@ extern "C" int ragb_store_build_filter(ragb_store* s, const uint8_t* src_allowed
   ON_DEVICE(s->device);
   const int64_t n = s->n.load(std::memory_order_acquire);
   if (out_total) *out_total = 0;
+  own_stream_waits(s);  // a search still running on a caller's stream may be reading the current mask
   s->filter_n = -1;
   if (n == 0) { s->filter_n = 0; return RAGB_OK; }
   RB_TRY(meta_reserve(s, n));
@@ -1162,6 +1183,7 @@ extern "C" int ragb_search_scatter_dev(ragb_store* s, const float* q, int64_t nq
     po.keys[r] = x->keys[r] + (size_t)x->rank * nq * kpad;  // this rank's [nq][kpad] slot in rank r's buffer
     po.flag[r] = x->flags[r] + x->rank;
   }
+  if (!stream) own_stream_waits(s);
   bool sf;
   RB_TRY(resolve_valid(s, &valid, row_end, &sf));
   s->peer = po;
@@ -1169,6 +1191,7 @@ extern "C" int ragb_search_scatter_dev(ragb_store* s, const float* q, int64_t nq
   s->peer = PeerOut{};
   if (rc != RAGB_OK) return rc;
   if (!stream) CU_TRY(cudaStreamSynchronize(st));
+  else mark_caller_search(s, st);
   return RAGB_OK;
 }
 
@@ -1192,10 +1215,12 @@ extern "C" int ragb_search_dev(ragb_store* s, const float* q, int64_t nq, int k,
   std::lock_guard<std::mutex> ls(s->search_mu);
   ON_DEVICE(s->device);
   cudaStream_t st = stream ? (cudaStream_t)stream : s->stream;
+  if (!stream) own_stream_waits(s);
   bool sf;
   RB_TRY(resolve_valid(s, &valid, row_end, &sf));
   RB_TRY(search_core(s, q, nq, k, metric, threshold, flags, row_begin, row_end, valid, 0, nullptr, out_scores, out_ids, st));
   if (!stream) CU_TRY(cudaStreamSynchronize(st));
+  else mark_caller_search(s, st);
   return RAGB_OK;
 }
 
@@ -1220,6 +1245,7 @@ extern "C" int ragb_search(ragb_store* s, const float* q, int64_t nq, int k, int
   char* d = (char*)s->io;
   char* h = (char*)s->pin;
   memcpy(h, q, qb);
+  own_stream_waits(s);
   CU_TRY(cudaMemcpyAsync(d, h, qb, cudaMemcpyHostToDevice, s->stream));
   if (valid) CU_TRY(cudaMemcpyAsync(d + o_v, valid, vb, cudaMemcpyHostToDevice, s->stream));
   RB_TRY(search_core(s, (const float*)d, nq, k, metric, threshold, flags, row_begin, row_end,
