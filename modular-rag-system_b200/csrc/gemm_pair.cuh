@@ -27,6 +27,7 @@ constexpr int kPairStagesSmall = 5;              // ring depth next to the share
 constexpr int kPairStagesLarge = 6;              // kpad 64 / 128: candidates live in global memory
 constexpr int kPairN = 256;                       // corpus rows per accumulator tile (both halves)
 constexpr int kPairStageBytes = 2 * kStageBytesA; // 16 KB queries + 16 KB half corpus tile
+constexpr int kPairSyncTiles = 8;                 // tiles between two meetings of the pairs that share a row split
 constexpr uint32_t kPeerBitMask = 0xFEFFFFFFu;    // shared::cluster address of the even (leader) CTA of a pair
 
 __device__ __forceinline__ void tma_load_2d_pair(void* dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1) {
@@ -306,6 +307,19 @@ gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_co
     uint32_t ph = 0;
     for (int64_t t = t0; t < t1; ++t) {
       const int row0 = (int)(p.row_begin + t * kPairN) + rank * (kPairN / 2);
+      // The pps pairs of a row split read the same rows; nothing else keeps them together, and once they drift
+      // further apart than L2 holds, every pair fetches the split from HBM by itself (measured: 22 - 40 GB read for
+      // 15.4 GB of corpus).  Every kPairSyncTiles tiles the leaders' producers meet at a counter in global memory;
+      // the ring is full at that point, so the tensor pipe keeps running while they wait.  Only enabled by the
+      // host when every CTA of the grid is resident at once.
+      if (p.sync_ctr != nullptr && rank == 0 && t > t0 && ((t - t0) % kPairSyncTiles) == 0) {
+        if (elect_one()) {
+          const unsigned target = (unsigned)pps * (unsigned)((t - t0) / kPairSyncTiles);
+          atomicAdd(&p.sync_ctr[split], 1u);
+          while (*reinterpret_cast<volatile unsigned*>(&p.sync_ctr[split]) < target) __nanosleep(64);
+        }
+        __syncwarp();
+      }
       for (int kb = 0; kb < n_kb; ++kb) {
         mbar_wait(&empty_bar[s], ph ^ 1);  // the leader's commit released this slot in both CTAs
         if (elect_one()) {

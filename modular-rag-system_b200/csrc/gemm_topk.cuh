@@ -360,12 +360,16 @@ struct GemmState {
   CUtensorMap map_x_pair;
   const void* pair_rows = nullptr;
   int64_t pair_capacity = -1;
+  void* sync_ctr = nullptr;        // per-split meeting counters of the pair kernel
+  size_t sync_ctr_bytes = 0;
   int pair_clusters[3] = {0, 0, 0};  // co-resident SM pairs per kernel variant (kpad <= 32, 64, 128)
   int occ_c = 0, occ_clusters = 0;
   size_t occ_smem = 0;
 };
 inline void gemm_state_free(GemmState* g) {
   if (g->qh) cudaFree(g->qh);
+  if (g->sync_ctr) cudaFree(g->sync_ctr);
+  g->sync_ctr = nullptr; g->sync_ctr_bytes = 0;
   g->qh = nullptr; g->qh_bytes = 0; g->map_rows = nullptr; g->map_capacity = -1;
   g->ts_rows = nullptr; g->ts_capacity = -1; g->ts_nt = 0;
   g->pair_rows = nullptr; g->pair_capacity = -1;

@@ -53,6 +53,8 @@ struct TsParams {
   uint64_t* out;        // [n_qt*128][n_splits][kpad] sorted keys
   uint64_t* cand_ws;    // pair kernel, kpad > 32: [grid][128][2*kpad] candidate buffers in global memory
   float sel_slack;      // pair kernel: slack under the user threshold for the 16-bit-query selection pass
+  unsigned* sync_ctr;   // pair kernel: [n_splits] zeroed per launch, or null — the SM pairs that stream the same row
+                        // split meet every kPairSyncTiles tiles so that they keep hitting each other's rows in L2
 };
 
 __device__ __forceinline__ void tma_load_2d_mc(void* dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1,

@@ -814,6 +814,14 @@ static int gemm_pair_launch(ragb_store* s, const float* q, int64_t nq, int k, in
   p.sel_slack = s->dtype == RAGB_BF16 ? 8e-3f : 2e-3f;
   p.id_base = 0;  // chunk keys carry LOCAL start rows; the re-score adds id_base
   p.idesc = umma_idesc(s->dtype == RAGB_BF16, 2 * kGemmM, kPairN);
+  // pairs of one split meet periodically (gemm_pair.cuh) — only when the whole grid is resident at once, else the
+  // meeting would wait for CTAs that cannot start
+  p.sync_ctr = nullptr;
+  if (pps > 1 && n_qt * splits <= 2 * g->pair_clusters[ei] && env_int("RAGB_PAIR_SYNC", 1)) {
+    RB_TRY(grow(&g->sync_ctr, &g->sync_ctr_bytes, 1024 * sizeof(unsigned), false));
+    CU_TRY(cudaMemsetAsync(g->sync_ctr, 0, (size_t)splits * sizeof(unsigned), st));
+    p.sync_ctr = (unsigned*)g->sync_ctr;
+  }
   const size_t part_bytes = (size_t)nq_pad * splits * kpad * sizeof(uint64_t);
   const size_t cand_bytes = E == 2 ? 0 : (size_t)n_qt * splits * kGemmM * (32 * E) * sizeof(uint64_t);
   RB_TRY(grow(&s->ws, &s->ws_bytes, part_bytes + cand_bytes, false));
