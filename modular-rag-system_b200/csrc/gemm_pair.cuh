@@ -27,7 +27,7 @@ constexpr int kPairStagesSmall = 5;              // ring depth next to the share
 constexpr int kPairStagesLarge = 6;              // kpad 64 / 128: candidates live in global memory
 constexpr int kPairN = 256;                       // corpus rows per accumulator tile (both halves)
 constexpr int kPairStageBytes = 2 * kStageBytesA; // 16 KB queries + 16 KB half corpus tile
-constexpr int kPairSyncTiles = 8;                 // tiles between two meetings of the pairs that share a row split
+constexpr int kPairSyncTiles = 8;                 // default tiles between two meetings of the pairs that share a row split
 constexpr uint32_t kPeerBitMask = 0xFEFFFFFFu;    // shared::cluster address of the even (leader) CTA of a pair
 
 __device__ __forceinline__ void tma_load_2d_pair(void* dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1) {
@@ -312,9 +312,9 @@ gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_co
       // 15.4 GB of corpus).  Every kPairSyncTiles tiles the leaders' producers meet at a counter in global memory;
       // the ring is full at that point, so the tensor pipe keeps running while they wait.  Only enabled by the
       // host when every CTA of the grid is resident at once.
-      if (p.sync_ctr != nullptr && rank == 0 && t > t0 && ((t - t0) % kPairSyncTiles) == 0) {
+      if (p.sync_ctr != nullptr && rank == 0 && t > t0 && ((t - t0) % p.sync_tiles) == 0) {
         if (elect_one()) {
-          const unsigned target = (unsigned)pps * (unsigned)((t - t0) / kPairSyncTiles);
+          const unsigned target = (unsigned)pps * (unsigned)((t - t0) / p.sync_tiles);
           atomicAdd(&p.sync_ctr[split], 1u);
           while (*reinterpret_cast<volatile unsigned*>(&p.sync_ctr[split]) < target) __nanosleep(64);
         }

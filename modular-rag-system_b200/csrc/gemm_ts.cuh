@@ -53,6 +53,7 @@ struct TsParams {
   uint64_t* out;        // [n_qt*128][n_splits][kpad] sorted keys
   uint64_t* cand_ws;    // pair kernel, kpad > 32: [grid][128][2*kpad] candidate buffers in global memory
   float sel_slack;      // pair kernel: slack under the user threshold for the 16-bit-query selection pass
+  int sync_tiles;       // pair kernel: tiles between two meetings
   unsigned* sync_ctr;   // pair kernel: [n_splits] zeroed per launch, or null — the SM pairs that stream the same row
                         // split meet every kPairSyncTiles tiles so that they keep hitting each other's rows in L2
 };

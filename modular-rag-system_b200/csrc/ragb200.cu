@@ -790,10 +790,12 @@ static int gemm_pair_launch(ragb_store* s, const float* q, int64_t nq, int k, in
     attr_set[ei] = true;
   }
   cudaLaunchConfig_t cfg = {};
-  cudaLaunchAttribute attr[1];
+  cudaLaunchAttribute attr[2];
   cfg.blockDim = dim3(kGemmThreads); cfg.dynamicSmemBytes = smem; cfg.stream = st;
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+  attr[1].id = cudaLaunchAttributeCooperative;  // only counted in numAttrs when the pairs meet (below)
+  attr[1].val.cooperative = 1;
   cfg.attrs = attr; cfg.numAttrs = 1;
   if (g->pair_clusters[ei] == 0) {
     cfg.gridDim = dim3((unsigned)(2 * (s->n_sm / 2)));
@@ -821,6 +823,7 @@ static int gemm_pair_launch(ragb_store* s, const float* q, int64_t nq, int k, in
     RB_TRY(grow(&g->sync_ctr, &g->sync_ctr_bytes, 1024 * sizeof(unsigned), false));
     CU_TRY(cudaMemsetAsync(g->sync_ctr, 0, (size_t)splits * sizeof(unsigned), st));
     p.sync_ctr = (unsigned*)g->sync_ctr;
+    p.sync_tiles = std::max(1, env_int("RAGB_PAIR_SYNC_TILES", kPairSyncTiles));
   }
   const size_t part_bytes = (size_t)nq_pad * splits * kpad * sizeof(uint64_t);
   const size_t cand_bytes = E == 2 ? 0 : (size_t)n_qt * splits * kGemmM * (32 * E) * sizeof(uint64_t);
@@ -830,7 +833,23 @@ static int gemm_pair_launch(ragb_store* s, const float* q, int64_t nq, int k, in
   cfg.gridDim = dim3((unsigned)(n_qt * splits));
   {
     ProfScope prof(s, st);
-    CU_TRY(cudaLaunchKernelEx(&cfg, kern, map_q, g->map_x_pair, p));
+    cudaError_t le = cudaErrorUnknown;
+    if (p.sync_ctr) {
+      // The meeting spins on CTAs of the same grid: it is only safe if the whole grid is resident at once.  A
+      // COOPERATIVE launch makes the driver guarantee that (all CTAs start together or the launch is refused),
+      // also against kernels of other streams / other stores that hold SMs at the moment.
+      // (RAGB_PAIR_COOP=0 drops the attribute: Nsight Compute's kernel replay cannot measure cooperative launches)
+      // Nsight Compute announces itself in the environment of the process it profiles.
+      const bool under_ncu = getenv("NV_COMPUTE_PROFILER_PERFWORKS_DIR") != nullptr;
+      cfg.numAttrs = env_int("RAGB_PAIR_COOP", under_ncu ? 0 : 1) ? 2 : 1;
+      le = cudaLaunchKernelEx(&cfg, kern, map_q, g->map_x_pair, p);
+      if (le != cudaSuccess) {  // refused (grid does not fit right now): launch without the meeting
+        (void)cudaGetLastError();
+        cfg.numAttrs = 1;
+        p.sync_ctr = nullptr;
+      }
+    }
+    if (le != cudaSuccess) CU_TRY(cudaLaunchKernelEx(&cfg, kern, map_q, g->map_x_pair, p));
   }
   LAUNCHED();
   return gemm_finish_chunks(s, q, nq, k, kpad, k_sel, metric, threshold, flags, rb, re, valid, id_base, p.out, splits,
