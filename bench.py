@@ -25,6 +25,7 @@ import os
 import subprocess
 import sys
 import tempfile
+import threading
 import time
 from pathlib import Path
 
@@ -170,8 +171,31 @@ class ClockSampler:
 
     def __init__(self, index: int):
         self.index, self.proc, self.path = index, None, None
+        self.nvml, self.nvml_thread, self.nvml_stop = [], None, threading.Event()
+
+    def _nvml_loop(self):
+        """In-process NVML samples (the calls nvidia-smi makes) every ~2 ms: a timed region of a few tens of
+        milliseconds ends before a freshly started nvidia-smi prints its first line."""
+        try:
+            import pynvml as nv
+            nv.nvmlInit()
+            h = nv.nvmlDeviceGetHandleByIndex(self.index)
+            mx = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
+            names = (("hw_slowdown", nv.nvmlClocksEventReasonHwSlowdown),
+                     ("hw_thermal_slowdown", nv.nvmlClocksEventReasonHwThermalSlowdown),
+                     ("sw_thermal_slowdown", nv.nvmlClocksEventReasonSwThermalSlowdown),
+                     ("sw_power_cap", nv.nvmlClocksEventReasonSwPowerCap))
+            while not self.nvml_stop.is_set():
+                r = nv.nvmlDeviceGetCurrentClocksEventReasons(h)
+                self.nvml.append((float(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)), float(mx),
+                                  [n for n, bit in names if r & bit]))
+                time.sleep(0.002)
+        except Exception:
+            pass
 
     def __enter__(self):
+        self.nvml_thread = threading.Thread(target=self._nvml_loop, daemon=True)
+        self.nvml_thread.start()
         try:
             f = tempfile.NamedTemporaryFile("w", suffix=".csv", delete=False)
             self.path = f.name
@@ -182,6 +206,9 @@ class ClockSampler:
         return self
 
     def __exit__(self, *a):
+        self.nvml_stop.set()
+        if self.nvml_thread is not None:
+            self.nvml_thread.join(timeout=2)
         if self.proc is not None:
             time.sleep(0.15)
             self.proc.terminate()
@@ -209,7 +236,12 @@ class ClockSampler:
         os.unlink(self.path)
         if sm:
             sm.sort()
-            out.update(sm_mhz=sm[len(sm) // 2], sm_max_mhz=max(mx), reasons=sorted(reasons), samples=len(sm))
+            out.update(sm_mhz=sm[len(sm) // 2], sm_max_mhz=max(mx), reasons=sorted(reasons), samples=len(sm),
+                       source="nvidia-smi -lms 20")
+        if self.nvml and out["samples"] < 3:
+            v = sorted(x[0] for x in self.nvml)
+            out.update(sm_mhz=v[len(v) // 2], sm_max_mhz=max(x[1] for x in self.nvml),
+                       reasons=sorted({n for x in self.nvml for n in x[2]}), samples=len(v), source="nvml, 2 ms period")
         return out
 
 
@@ -293,6 +325,12 @@ def roofline_obj(kind, store, work_per_launch, pk, pk_src, sustained):
             (", sustained" if (kind == "tensor" and sustained) else ", burst" if kind == "tensor" else "")}
 
 
+def bound_of(B, pk):
+    """Which roofline bounds a search over 16-bit rows at batch B: every row is read once (2 B per element) and
+    costs 2*B flop per element, so the tensor pipe binds above B = peak_flops / peak_bytes (about 250 here)."""
+    return "tensor" if B * float(pk["hbm_gbs"]) * 1e9 > float(pk["bf16_tflops"]) * 1e12 else "hbm"
+
+
 def attach_traffic(roof, key):
     """roofline.traffic = dram bytes read+written per launch of that kernel from the committed `ncu --set full` capture."""
     try:
@@ -346,7 +384,7 @@ def run_b200(args):
     clocks = cs.summary()
     qps = B * args.steps / (ms / 1e3)
     # roofline of the dominant kernel (this rank's shard): its event brackets were armed for exactly these steps
-    tensor_path = B >= 4
+    tensor_path = bound_of(B, pk) == "tensor"
     work = 2.0 * B * (r1 - r0) * d if tensor_path else float(r1 - r0) * d * 2
     roof = roofline_obj("tensor" if tensor_path else "hbm", store, work, pk, pk_src, sustained=(ms / args.steps > 50.0))
 
@@ -412,7 +450,7 @@ def run_extras(args, pkg, torch, store, wl, pk, pk_src):
         fn = (lambda: st.search_dev(Q, args.k, "ip"))
         steps = 50 if B == 1 else args.steps
         ms = time_device(torch, None, fn, steps, args.warmup, 1, after_warmup=lambda: st.profile(True))
-        tensor = B >= 4
+        tensor = bound_of(B, pk) == "tensor"
         work = 2.0 * B * len(st) * w["d"] if tensor else float(len(st)) * w["d"] * 2
         roof = roofline_obj("tensor" if tensor else "hbm", st, work, pk, pk_src, sustained=False)
         roof["kernel_share_of_step"] = roof["kernel_ms"] / (ms / steps)

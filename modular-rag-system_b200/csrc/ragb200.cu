@@ -645,12 +645,15 @@ static int env_int(const char* name, int dflt) {
 }
 static bool pair_enabled() { return env_int("RAGB_PAIR", 1) && !env_int("RAGB_GEMM_SS", 0) && !env_int("RAGB_TS", 0); }
 
-static bool gemm_eligible(const ragb_store* s, int64_t nq, int k, int flags) {
+static bool gemm_eligible(const ragb_store* s, int64_t nq, int k, int flags, int64_t n_rows) {
   if (s->dtype == RAGB_F32 || (flags & RAGB_FORCE_SCAN)) return false;
   const int kp = kpad_of(k);
   // kpad 64 / 128 exists only in the SM-pair kernel (needs two 128-query tiles)
   if (kp > kGemmMaxKpad) return kp <= 128 && nq > kGemmM && pair_enabled() && !(flags & RAGB_NO_RESCORE);
-  return (flags & RAGB_FORCE_GEMM) || nq >= 4;
+  if ((flags & RAGB_FORCE_GEMM) || nq >= 4) return true;
+  // 2 or 3 queries: the scan kernel walks the rows once PER QUERY, which is free while the window sits in L2 and
+  // costs a full HBM pass each beyond it (10M x 768: 4.26 / 6.38 ms against 2.23 ms for one tensor-path pass)
+  return nq >= 2 && n_rows * s->ld * 2 >= (int64_t)64 << 20;
 }
 
 template <typename T>
@@ -759,7 +762,7 @@ static int gemm_pair_launch(ragb_store* s, const float* q, int64_t nq, int k, in
   const int n_kb = (s->dim + kGemmKB - 1) / kGemmKB;
   int n_qt = (int)((nq + kGemmM - 1) / kGemmM);
   // the pair kernel selects CHUNKS of 32 rows; the fp32 re-score resolves them to rows, so it cannot be skipped
-  if (n_qt < 2 || (flags & RAGB_NO_RESCORE)) return RAGB_EUNSUPPORTED;
+  if ((n_qt < 2 && !env_int("RAGB_PAIR_SMALL", 0)) || (flags & RAGB_NO_RESCORE)) return RAGB_EUNSUPPORTED;
   n_qt += n_qt & 1;  // an odd tile count gets one all-zero query tile
   const int64_t nq_pad = (int64_t)n_qt * kGemmM;
   if (g->pair_rows != s->rows || g->pair_capacity != s->capacity) {
@@ -1044,7 +1047,7 @@ static int search_core(ragb_store* s, const float* q, int64_t nq, int k, int met
   const int kpad = kpad_of(k);
   if (re - rb <= 0)  // empty store / empty window: RAGResult([], []) (:517-521)
     return merge_launch(nullptr, nq, 0, kpad, 0, 0, k, out_scores, out_ids, out_keys, st, false, &s->peer);
-  if (gemm_eligible(s, nq, k, flags))
+  if (gemm_eligible(s, nq, k, flags, re - rb))
     return gemm_search(s, q, nq, k, metric, threshold, flags, rb, re, valid, id_base, out_keys, out_scores, out_ids, st);
   ScanParams p;
   p.X = s->rows; p.ld = s->ld; p.dim = s->dim; p.row_begin = rb; p.row_end = re; p.valid = valid;

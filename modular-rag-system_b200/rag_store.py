@@ -345,6 +345,14 @@ class B200VectorStore:
         docs = list(documents)
         ok = [False] * len(docs)
         rows, items, idx = [], [], []
+        many = getattr(self.embedding_generator, "generate_embeddings", None)
+        if many is not None:  # a batched embedder (embedder.py): one encoder + pooling pass for the whole batch
+            need = [d for d in docs if not d.embedding]
+            try:
+                for d, e in zip(need, many([d.content for d in need]) if need else []):
+                    d.embedding = e
+            except Exception as e:
+                print(f"Error generating embeddings: {e}")
         for i, d in enumerate(docs):
             try:
                 if not d.embedding:  # :311-312
@@ -484,6 +492,13 @@ class B200VectorStore:
         out: List[Any] = [None] * len(queries)
         groups: Dict[tuple, List[int]] = {}
         embs: List[Optional[List[float]]] = []
+        many = getattr(self.embedding_generator, "generate_embeddings", None)
+        if embeddings is None and many is not None and len(queries):
+            try:
+                embeddings = many([qy.query_text for qy in queries])
+            except Exception as ex:
+                print(f"Device search error: {ex}")
+                embeddings = None
         for i, qy in enumerate(queries):
             try:
                 e = embeddings[i] if embeddings is not None else self.embedding_generator.generate_embedding(qy.query_text)

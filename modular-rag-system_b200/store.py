@@ -320,5 +320,30 @@ def gather_merge_dev(exchange, nq: int, k: int, device: int, status=None, out=No
     return ids, scores
 
 
+def pool_norm_pack_dev(tok, mask, out_dtype: str = "fp32"):
+    """Stateless K1 (csrc/ingest.cuh): masked mean over tokens -> L2 normalise -> pack, torch CUDA tensors in and out.
+    tok [B,S,H] fp16/bf16/fp32 contiguous, mask [B,S] (u8/bool/i32/i64/f32) or None.  Returns (rows [B,H] of
+    ``out_dtype``, norms [B] fp32 — the norm of the pooled vector before normalising; 0 marks an all-masked chunk).
+    Replaces the tail of ``SentenceTransformer.encode`` (embedding_pipeline.py:424, ollama_rag_system.py:163)."""
+    import torch
+    if tok.dim() != 3 or not tok.is_contiguous() or not tok.is_cuda:
+        raise ValueError("token embeddings must be a contiguous CUDA tensor [B,S,H]")
+    B, S, H = tok.shape
+    mp, mc = None, 0
+    if mask is not None:
+        if tuple(mask.shape) != (B, S) or not mask.is_contiguous():
+            raise ValueError("mask must be contiguous [B,S]")
+        mp, mc = mask.data_ptr(), _torch_mask_code(mask)
+    tdt = {"fp16": torch.float16, "bf16": torch.bfloat16, "fp32": torch.float32}[out_dtype]
+    ld = (H + 7) // 8 * 8
+    dev = tok.device.index or 0
+    out = torch.empty((B, ld), dtype=tdt, device=tok.device)
+    norms = torch.empty((B,), dtype=torch.float32, device=tok.device)
+    if B:
+        check(lib().ragb_pool_norm_pack_dev(dev, tok.data_ptr(), _torch_code(tok), mp, mc, B, S, H, out.data_ptr(),
+                                            _DTYPES[out_dtype], ld, norms.data_ptr(), _cur_stream(dev)))
+    return out[:, :H], norms
+
+
 def launch_count() -> int:
     return int(lib().ragb_launch_count())
