@@ -143,12 +143,56 @@ __global__ void __launch_bounds__(kMergeThreads, 3) finish_chunks_kernel(const F
     scale = qq > 0.f ? rsqrtf(qq) : 0.f;  // zero query scores 0.0 everywhere, :214-215
   }
   __syncthreads();
-  for (int i = threadIdx.x; i < n_keys; i += kMergeThreads) {
+  // Bound first: the first m keys of every list (m * n_lists >= k_sel of them) contain at least k_sel keys at or above
+  // their k_sel-th largest, L, so the k_sel best keys overall are all >= L and only those need a rank.  With many
+  // short lists (a single query tile is split 74 ways) that is a few dozen keys instead of thousands, each of which
+  // would otherwise be binary-searched through every list.
+  __shared__ unsigned long long s_bound;
+  __shared__ int s_ncand;
+  // (with a handful of long lists the binary searches below are as cheap: the bound pays from ~8 lists up)
+  const bool bounded = p.n_lists > 8;
+  if (threadIdx.x == 0) { s_bound = 0ull; s_ncand = bounded ? 0 : 0x40000000; }
+  __syncthreads();
+  if (bounded) {
+    const int m = min(p.kpad, (p.k_sel + p.n_lists - 1) / p.n_lists);
+    const int hs = m * p.n_lists;
+    for (int i = threadIdx.x; i < hs; i += kMergeThreads) {
+      const uint64_t key = lists[(i / m) * p.kpad + (i % m)];
+      if (key == 0) continue;
+      int rank = 0;
+      for (int l = 0; l < p.n_lists; ++l)
+        for (int t = 0; t < m; ++t) rank += lists[l * p.kpad + t] > key ? 1 : 0;
+      if (rank == p.k_sel - 1) s_bound = key;
+    }
+  }
+  __syncthreads();
+  const uint64_t bound = s_bound;  // 0: fewer than k_sel keys among the heads — everything is a candidate
+  uint64_t* cand = surv;           // free until step 2
+  const int cand_cap = p.kpad * kFinishMaxChunkRows;
+  for (int i = threadIdx.x; bounded && i < n_keys; i += kMergeThreads) {
     const uint64_t key = lists[i];
-    if (key == 0) continue;
-    int rank = 0;
-    for (int l = 0; l < p.n_lists && rank < p.k_sel; ++l) rank += count_greater_sorted(lists + l * p.kpad, p.kpad, key);
-    if (rank < p.k_sel) chunk[rank] = key;
+    if (key != 0 && key >= bound) {
+      const int pos = atomicAdd(&s_ncand, 1);
+      if (pos < cand_cap) cand[pos] = key;
+    }
+  }
+  __syncthreads();
+  const int n_cand1 = s_ncand;
+  if (n_cand1 <= cand_cap) {
+    for (int i = threadIdx.x; i < n_cand1; i += kMergeThreads) {
+      const uint64_t key = cand[i];
+      int rank = 0;
+      for (int j = 0; j < n_cand1; ++j) rank += cand[j] > key ? 1 : 0;
+      if (rank < p.k_sel) chunk[rank] = key;
+    }
+  } else {  // more candidates than fit: rank every key by binary search in each sorted list
+    for (int i = threadIdx.x; i < n_keys; i += kMergeThreads) {
+      const uint64_t key = lists[i];
+      if (key == 0) continue;
+      int rank = 0;
+      for (int l = 0; l < p.n_lists && rank < p.k_sel; ++l) rank += count_greater_sorted(lists + l * p.kpad, p.kpad, key);
+      if (rank < p.k_sel) chunk[rank] = key;
+    }
   }
   __syncthreads();
 

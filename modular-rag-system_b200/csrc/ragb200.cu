@@ -648,8 +648,8 @@ static bool pair_enabled() { return env_int("RAGB_PAIR", 1) && !env_int("RAGB_GE
 static bool gemm_eligible(const ragb_store* s, int64_t nq, int k, int flags, int64_t n_rows) {
   if (s->dtype == RAGB_F32 || (flags & RAGB_FORCE_SCAN)) return false;
   const int kp = kpad_of(k);
-  // kpad 64 / 128 exists only in the SM-pair kernel (needs two 128-query tiles)
-  if (kp > kGemmMaxKpad) return kp <= 128 && nq > kGemmM && pair_enabled() && !(flags & RAGB_NO_RESCORE);
+  // kpad 64 / 128 exists only in the SM-pair kernel
+  if (kp > kGemmMaxKpad && !(kp <= 128 && pair_enabled() && !(flags & RAGB_NO_RESCORE))) return false;
   if ((flags & RAGB_FORCE_GEMM) || nq >= 4) return true;
   // 2 or 3 queries: the scan kernel walks the rows once PER QUERY, which is free while the window sits in L2 and
   // costs a full HBM pass each beyond it (10M x 768: 4.26 / 6.38 ms against 2.23 ms for one tensor-path pass)
@@ -762,8 +762,8 @@ static int gemm_pair_launch(ragb_store* s, const float* q, int64_t nq, int k, in
   const int n_kb = (s->dim + kGemmKB - 1) / kGemmKB;
   int n_qt = (int)((nq + kGemmM - 1) / kGemmM);
   // the pair kernel selects CHUNKS of 32 rows; the fp32 re-score resolves them to rows, so it cannot be skipped
-  if ((n_qt < 2 && !env_int("RAGB_PAIR_SMALL", 0)) || (flags & RAGB_NO_RESCORE)) return RAGB_EUNSUPPORTED;
-  n_qt += n_qt & 1;  // an odd tile count gets one all-zero query tile
+  if (flags & RAGB_NO_RESCORE) return RAGB_EUNSUPPORTED;
+  n_qt += n_qt & 1;  // an odd tile count (a single tile included) gets one all-zero query tile
   const int64_t nq_pad = (int64_t)n_qt * kGemmM;
   if (g->pair_rows != s->rows || g->pair_capacity != s->capacity) {
     RB_TRY(make_map(g, &g->map_x_pair, s->dtype, s->rows, s->dim, s->capacity, s->ld, kPairN / 2));
@@ -963,8 +963,19 @@ static int gemm_search(ragb_store* s, const float* q, int64_t nq, int k, int met
                        int64_t rb, int64_t re, const uint8_t* valid, uint32_t id_base, uint64_t* out_keys,
                        float* out_scores, int64_t* out_ids, cudaStream_t st) {
   if (pair_enabled()) {
-    int r = gemm_pair_search(s, q, nq, k, metric, threshold, flags, rb, re, valid, id_base, out_keys, out_scores, out_ids, st);
-    if (r != RAGB_EUNSUPPORTED) return r;
+    // One query tile (B <= 128): the pair kernel runs it beside an all-zero tile, i.e. at half its tensor rate, but its
+    // chunk-granular epilogue has no warm-up; the single-CTA kernel wastes nothing and streams at ~85 % of HBM peak, but
+    // pays ~0.4 ms of row-granular insertions while thresholds are loose.  Measured crossover: N*D around 8e9
+    // (1M x 384, B=128: 0.27 vs 0.64 ms; 10M x 768: 2.99 vs 2.90 ms).  RAGB_PAIR_SMALL=0/1 forces either.
+    bool want = true;
+    if (nq <= kGemmM && kpad_of(k) <= kGemmMaxKpad) {
+      const int force = env_int("RAGB_PAIR_SMALL", -1);
+      want = force >= 0 ? force != 0 : (double)(re - rb) * s->dim < 4e9;
+    }
+    if (want) {
+      int r = gemm_pair_search(s, q, nq, k, metric, threshold, flags, rb, re, valid, id_base, out_keys, out_scores, out_ids, st);
+      if (r != RAGB_EUNSUPPORTED) return r;
+    }
   }
   if (!env_int("RAGB_GEMM_SS", 0)) {
     int r = gemm_ts_search(s, q, nq, k, metric, threshold, flags, rb, re, valid, id_base, out_keys, out_scores, out_ids, st);

@@ -194,3 +194,34 @@ def test_full_size_properties_headline_shapes(n, d, dtype, nq, k):
     assert (ids2.cpu().numpy() == ids[:3]).mean() > 0.95
     assert np.abs(sc2.cpu().numpy() - sc[:3]).max() < tol
     s.close()
+
+
+@pytest.mark.parametrize("nq,k", [(4, 10), (17, 5), (128, 32), (40, 100), (2, 64)])
+def test_single_tile_batches_on_both_kernels(nq, k, monkeypatch):
+    """B <= 128 is one query tile: below the measured crossover it runs on the SM-pair kernel beside an all-zero tile
+    (chunk-granular epilogue), above it on the single-CTA kernel (csrc/ragb200.cu, gemm_search).  Both must agree with
+    the oracle; RAGB_PAIR_SMALL forces either.  k > 32 exists only on the pair kernel."""
+    import modular_rag_system_b200 as pkg
+    FORCE_GEMM, _, _ = _flags()
+    rng = np.random.default_rng(nq * 1000 + k)
+    n, dim = 30000, 384
+    X = rng.standard_normal((n, dim)).astype(np.float32)
+    Q = rng.standard_normal((nq, dim)).astype(np.float32)
+    Q[0] = X[4321] + 0.3 * rng.standard_normal(dim).astype(np.float32)
+    s = _store(X, "fp16")
+    got = {}
+    for force in ("1", "0"):
+        monkeypatch.setenv("RAGB_PAIR_SMALL", force)
+        l0 = pkg.launch_count()
+        ids, sc = s.search(Q, k, "cosine", flags=FORCE_GEMM)
+        launches = pkg.launch_count() - l0
+        _check(ids, sc, X, Q, k, "cosine", -np.inf, False, TOL["fp16"])
+        assert ids[0][0] == 4321
+        got[force] = (ids, sc, launches)
+    assert got["1"][2] == 3                      # convert + pair kernel + finish
+    if k <= 32:
+        assert got["0"][2] > 3                   # convert + single-CTA kernel + merge + re-score + merge
+        np.testing.assert_allclose(got["0"][1], got["1"][1], atol=2e-3)
+    monkeypatch.delenv("RAGB_PAIR_SMALL")
+    ids, sc = s.search(Q, k, "cosine")           # default routing
+    _check(ids, sc, X, Q, k, "cosine", -np.inf, False, TOL["fp16"])
