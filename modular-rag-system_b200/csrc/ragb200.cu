@@ -270,7 +270,15 @@ static int norm_pack_launch(const void* in, int64_t n, int dim, int64_t ld_in, v
   const bool vec_ok = ((uintptr_t)in % 16 == 0) && ((ld_in * sizeof(Tin)) % 16 == 0);
   const int rows_per_cta = 8;
   const int64_t grid = (n + rows_per_cta - 1) / rows_per_cta;
-  norm_pack_kernel<Tin, Tout><<<(unsigned)grid, 256, 0, st>>>((const Tin*)in, n, dim, ld_in, (Tout*)out, ld_out, norms, vec_ok);
+  const int64_t chunks = std::max<int64_t>((dim + 7) / 8, ld_out / 8);
+  static const bool generic_only = getenv("RAGB_NORM_PACK_GENERIC") != nullptr;  // A/B runs
+#define NP_ARGS (const Tin*)in, n, dim, ld_in, (Tout*)out, ld_out, norms, vec_ok
+  if (generic_only || chunks > 128) norm_pack_kernel<Tin, Tout><<<(unsigned)grid, 256, 0, st>>>(NP_ARGS);
+  else if (chunks <= 32) norm_pack_reg_kernel<Tin, Tout, 1><<<(unsigned)grid, 256, 0, st>>>(NP_ARGS);
+  else if (chunks <= 64) norm_pack_reg_kernel<Tin, Tout, 2><<<(unsigned)grid, 256, 0, st>>>(NP_ARGS);
+  else if (chunks <= 96) norm_pack_reg_kernel<Tin, Tout, 3><<<(unsigned)grid, 256, 0, st>>>(NP_ARGS);
+  else norm_pack_reg_kernel<Tin, Tout, 4><<<(unsigned)grid, 256, 0, st>>>(NP_ARGS);
+#undef NP_ARGS
   LAUNCHED();
   return RAGB_OK;
 }
