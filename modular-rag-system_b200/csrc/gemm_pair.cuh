@@ -80,10 +80,19 @@ __device__ __forceinline__ void mbar_wait_cluster(uint64_t* bar, uint32_t parity
 //   E == 4 : kpad == 64, E == 8 : kpad == 128 — 32*E slots in GLOBAL memory (L2 resident; an insert is a rare
 //            event, about k*ln(rows/k) per query over a CTA's lifetime), pruned by a register bitonic sort
 constexpr int kPairCapSmall = 64;
-template <int E> struct CandCfg {
-  static constexpr int cap = E == 2 ? kPairCapSmall : 32 * E;
-  static constexpr int stride = E == 2 ? kPairCapSmall + 1 : 32 * E;  // +1: conflict-free for both access patterns
+constexpr int kPairCapSmallQ = 48;  // next to a resident query tile: k <= 32 survivors + the 16 chunks one tile can add
+template <int E, bool Q = false> struct CandCfg {
+  static constexpr int cap = E == 2 ? (Q ? kPairCapSmallQ : kPairCapSmall) : 32 * E;
+  static constexpr int stride = E == 2 ? cap + 1 : 32 * E;  // +1: conflict-free for both access patterns
 };
+// Resident query tile (kQRes): when the 128 x dim query tile of a CTA fits in shared memory next to the ring
+// (dim <= 384: 6 k-blocks of 16 KB), it is loaded ONCE and the ring carries corpus k-blocks only.  Streaming the
+// query k-block with every corpus k-block doubles the L2 -> SM bytes (measured at 12.5M x 384, B=4096, top-100:
+// 154 GB per launch over the crossbar = 15.6 TB/s at full tensor rate, more than L2 delivers; the MMA warp waited
+// for TMA 22 % of the time, tensor pipe 60 % active).  With the tile resident the ring moves 16 KB per k-block.
+constexpr int kPairQResMaxKB = 6;
+constexpr int kPairStagesSmallQ = 5;   // x 16 KB, next to 96 KB of queries and the 49 KB of candidate buffers
+constexpr int kPairStagesLargeQ = 8;   // x 16 KB, next to 96 KB of queries
 // rows behind one candidate key.  k <= 32 (E == 2): 16 — half of one tcgen05.ld of 32 columns; the finish kernel then
 // re-reads half as many rows (1M x 384, B=1024: 133 -> 96 us).  k > 32: 32 — twice the chunks would double the
 // inserts into the global-memory buffers, which costs more than the finish kernel saves (1M x 384 top-100: +8 %).
@@ -218,9 +227,9 @@ __device__ __forceinline__ void epi_chunk(EpiCtx& e, uint32_t (&r)[32], int64_t 
   }
 }
 // once per tile (a query gains at most kPairN / rows-per-chunk = 16 or 8 chunks per tile): prune the buffers that could overflow next tile
-template <int E>
+template <int E, bool Q>
 __device__ __forceinline__ void epi_prune(EpiCtx& e, const TsParams& p, int lane) {
-  constexpr int kCap = CandCfg<E>::cap, kStride = CandCfg<E>::stride;
+  constexpr int kCap = CandCfg<E, Q>::cap, kStride = CandCfg<E, Q>::stride;
   unsigned need = __ballot_sync(0xffffffffu, e.cnt > kCap - kPairN / ChunkCfg<E>::rows);
   while (need) {
     const int j = __ffs(need) - 1;
@@ -237,9 +246,9 @@ __device__ __forceinline__ void epi_prune(EpiCtx& e, const TsParams& p, int lane
   }
 }
 // sort every query's survivors and write kpad keys
-template <int E>
+template <int E, bool Q>
 __device__ __forceinline__ void epi_flush(EpiCtx& e, int64_t qrow0, int split, const TsParams& p, int lane) {
-  constexpr int kStride = CandCfg<E>::stride;
+  constexpr int kStride = CandCfg<E, Q>::stride;
   __syncwarp();
   for (int j = 0; j < 32; ++j) {
     const int n = __shfl_sync(0xffffffffu, e.cnt, j);
@@ -260,22 +269,26 @@ __device__ __forceinline__ void epi_flush(EpiCtx& e, int64_t qrow0, int split, c
   }
 }
 
-template <int E, int kPairStages>
+template <int E, int kPairStages, bool kQRes = false>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_x,
                       const TsParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
-  // carve: stages | candidate buffers | barriers | tmem base     (identical offsets in both CTAs)
+  // carve: [resident query k-blocks] | stages | candidate buffers | barriers | tmem base   (identical offsets in both CTAs)
+  typedef CandCfg<E, kQRes> Cand;
+  constexpr int kStageB = kQRes ? kStageBytesA : kPairStageBytes;  // bytes per ring stage
   uint8_t* smem = reinterpret_cast<uint8_t*>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
-  uint8_t* stage_base = smem;
-  uint64_t* cand_smem = reinterpret_cast<uint64_t*>(smem + (size_t)kPairStages * kPairStageBytes);
-  uint64_t* bars = cand_smem + (E == 2 ? (size_t)kGemmM * CandCfg<E>::stride : 0);
-  uint64_t* cand = E == 2 ? cand_smem : p.cand_ws + (size_t)blockIdx.x * kGemmM * CandCfg<E>::stride;
+  uint8_t* q_base = smem;
+  uint8_t* stage_base = smem + (kQRes ? (size_t)p.n_kb * kStageBytesA : 0);
+  uint64_t* cand_smem = reinterpret_cast<uint64_t*>(stage_base + (size_t)kPairStages * kStageB);
+  uint64_t* bars = cand_smem + (E == 2 ? (size_t)kGemmM * Cand::stride : 0);
+  uint64_t* cand = E == 2 ? cand_smem : p.cand_ws + (size_t)blockIdx.x * kGemmM * Cand::stride;
   uint64_t* full_bar = bars;                     // leader's copy is the one in use
   uint64_t* empty_bar = bars + kPairStages;      // one per CTA
   uint64_t* tfull_bar = bars + 2 * kPairStages;  // one per CTA
   uint64_t* tempty_bar = tfull_bar + 2;          // leader's copy is the one in use
-  uint32_t* tmem_base_smem = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+  uint64_t* q_bar = tempty_bar + 2;              // kQRes: the query tiles of both CTAs have landed (leader's copy)
+  uint32_t* tmem_base_smem = reinterpret_cast<uint32_t*>(q_bar + 1);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int rank = blockIdx.x & 1;               // cluster dims (2,1,1): rank == %cluster_ctarank
@@ -288,6 +301,7 @@ gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_co
   if (threadIdx.x == 0) {
     for (int i = 0; i < kPairStages; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
     for (int i = 0; i < 2; ++i) { mbar_init(&tfull_bar[i], 1); mbar_init(&tempty_bar[i], 8); }
+    mbar_init(q_bar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) {  // the same warp of BOTH CTAs allocates for the pair
@@ -305,6 +319,14 @@ gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_co
     const int q_row = qt * kGemmM;
     int s = 0;
     uint32_t ph = 0;
+    if constexpr (kQRes) {
+      if (t0 < t1 && elect_one()) {
+        if (rank == 0) mbar_expect_tx(q_bar, 2u * (uint32_t)n_kb * kStageBytesA);  // both CTAs' tiles land on the leader
+        for (int kb = 0; kb < n_kb; ++kb)
+          tma_load_2d_pair(q_base + (size_t)kb * kStageBytesA, &map_q, q_bar, kb * kGemmKB, q_row);
+      }
+      __syncwarp();
+    }
     for (int64_t t = t0; t < t1; ++t) {
       const int row0 = (int)(p.row_begin + t * kPairN) + rank * (kPairN / 2);
       // The pps pairs of a row split read the same rows; nothing else keeps them together, and once they drift
@@ -323,10 +345,14 @@ gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_co
       for (int kb = 0; kb < n_kb; ++kb) {
         mbar_wait(&empty_bar[s], ph ^ 1);  // the leader's commit released this slot in both CTAs
         if (elect_one()) {
-          if (rank == 0) mbar_expect_tx(&full_bar[s], 2u * kPairStageBytes);  // both CTAs' bytes land on the leader
-          uint8_t* d = stage_base + (size_t)s * kPairStageBytes;
-          tma_load_2d_pair(d, &map_q, &full_bar[s], kb * kGemmKB, q_row);
-          tma_load_2d_pair(d + kStageBytesA, &map_x, &full_bar[s], kb * kGemmKB, row0);
+          if (rank == 0) mbar_expect_tx(&full_bar[s], 2u * kStageB);  // both CTAs' bytes land on the leader
+          uint8_t* d = stage_base + (size_t)s * kStageB;
+          if constexpr (kQRes) {
+            tma_load_2d_pair(d, &map_x, &full_bar[s], kb * kGemmKB, row0);
+          } else {
+            tma_load_2d_pair(d, &map_q, &full_bar[s], kb * kGemmKB, q_row);
+            tma_load_2d_pair(d + kStageBytesA, &map_x, &full_bar[s], kb * kGemmKB, row0);
+          }
         }
         if (++s == kPairStages) { s = 0; ph ^= 1; }
       }
@@ -336,8 +362,12 @@ gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_co
     if (rank == 0) {
       const uint32_t idesc = p.idesc;
       const uint64_t desc0 = umma_desc_sw128(smem_u32(stage_base));
+      const uint64_t descq = umma_desc_sw128(smem_u32(q_base));
       int s = 0;
       uint32_t ph = 0, acc = 0, aph = 0;
+      if constexpr (kQRes) {
+        if (t0 < t1) { mbar_wait(q_bar, 0); tc_fence_after(); }
+      }
       for (int64_t t = t0; t < t1; ++t) {
         mbar_wait_cluster(&tempty_bar[acc], aph ^ 1);  // both CTAs' epilogues drained this accumulator
         tc_fence_after();
@@ -346,8 +376,9 @@ gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_co
           mbar_wait(&full_bar[s], ph);
           tc_fence_after();
           if (elect_one()) {
-            const uint64_t adesc = desc0 + (uint64_t)((uint32_t)s * (kPairStageBytes >> 4));
-            const uint64_t bdesc = adesc + (kStageBytesA >> 4);
+            const uint64_t sdesc = desc0 + (uint64_t)((uint32_t)s * (kStageB >> 4));
+            const uint64_t adesc = kQRes ? descq + (uint64_t)((uint32_t)kb * (kStageBytesA >> 4)) : sdesc;
+            const uint64_t bdesc = kQRes ? sdesc : sdesc + (kStageBytesA >> 4);
 #pragma unroll
             for (int k4 = 0; k4 < kGemmKB / 16; ++k4)
               tc_mma_f16_pair(d_tmem, adesc + (uint64_t)(k4 * 2), bdesc + (uint64_t)(k4 * 2), idesc, (kb | k4) != 0);
@@ -365,8 +396,8 @@ gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_co
     const int tid = quarter * 32 + lane;
     const uint32_t lane_base = tmem_base + ((uint32_t)(quarter * 32) << 16);
     EpiCtx e;
-    e.my = cand + (size_t)tid * CandCfg<E>::stride;
-    e.warp_cand = cand + (size_t)(quarter * 32) * CandCfg<E>::stride;
+    e.my = cand + (size_t)tid * Cand::stride;
+    e.warp_cand = cand + (size_t)(quarter * 32) * Cand::stride;
     e.cnt = 0;
     // rows of the query tile past nq are zero padding: they must never take the candidate path
     // the 16-bit-query scores only SELECT: the user threshold is applied with slack here, exactly by the re-score
@@ -406,9 +437,9 @@ gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_co
       __syncwarp();
       if (lane == 0) mbar_arrive_cta(&tempty_bar[acc], 0);
       if ((acc ^= 1) == 0) aph ^= 1;
-      epi_prune<E>(e, p, lane);  // after the accumulator is handed back: off the MMA's critical path
+      epi_prune<E, kQRes>(e, p, lane);  // after the accumulator is handed back: off the MMA's critical path
     }
-    epi_flush<E>(e, (int64_t)qt * kGemmM + quarter * 32, split, p, lane);
+    epi_flush<E, kQRes>(e, (int64_t)qt * kGemmM + quarter * 32, split, p, lane);
   }
 
   tc_fence_before();

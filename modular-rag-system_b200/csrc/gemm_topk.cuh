@@ -362,7 +362,7 @@ struct GemmState {
   int64_t pair_capacity = -1;
   void* sync_ctr = nullptr;        // per-split meeting counters of the pair kernel
   size_t sync_ctr_bytes = 0;
-  int pair_clusters[3] = {0, 0, 0};  // co-resident SM pairs per kernel variant (kpad <= 32, 64, 128)
+  int pair_clusters[6] = {0, 0, 0, 0, 0, 0};  // co-resident SM pairs per kernel variant (kpad <= 32, 64, 128)
   int occ_c = 0, occ_clusters = 0;
   size_t occ_smem = 0;
 };

@@ -97,51 +97,64 @@ __global__ void __launch_bounds__(256) norm_pack_kernel(const Tin* __restrict__ 
   if (lane == 0 && norms) norms[row] = nrm;
 }
 
-// K2, rows of at most 256*CPL elements: the row is fetched ONCE (streaming 128-bit loads, all CPL of a lane
-// issued before the first is used) and stays in registers between the sum of squares and the divide.  Same
-// summation order as the generic kernel above (lane-serial over its chunks, then the shuffle tree), so both
-// produce the same bits.
-template <typename Tin, typename Tout, int CPL>
+// K2, rows of at most 256*CPL elements: a warp takes R consecutive rows, fetches each ONCE (streaming 128-bit loads,
+// all R*CPL of a lane issued before the first is used) and keeps them in registers between the sum of squares and
+// the divide.  R is chosen by the host so that a lane has 64-128 bytes in flight (16-bit rows of 384 elements are
+// only 768 bytes: one row per warp left HBM at half rate).  Same summation order per row as the generic kernel
+// above (lane-serial over its chunks, then the shuffle tree), so both produce the same bits.
+template <typename Tin, typename Tout, int CPL, int R>
 __global__ void __launch_bounds__(256) norm_pack_reg_kernel(const Tin* __restrict__ in, int64_t n, int dim,
                                                             int64_t ld_in, Tout* __restrict__ out,
                                                             int64_t ld_out, float* __restrict__ norms,
                                                             bool vec_ok) {
   const int lane = threadIdx.x & 31;
-  const int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-  if (row >= n) return;
-  const Tin* src = in + row * ld_in;
-  Tout* dst = out + row * ld_out;
+  const int64_t row0 = ((int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) * R;
+  if (row0 >= n) return;
   const int chunks_in = (dim + 7) / 8, chunks_out = (int)(ld_out / 8);
-  float f[CPL][8];
+  float f[R][CPL][8];
 #pragma unroll
-  for (int j = 0; j < CPL; ++j) {
-    const int c = lane + 32 * j;
-    if (c < chunks_in) load8_stream(src, c, dim, vec_ok, f[j]);
-    else {
+  for (int r = 0; r < R; ++r) {
+    const Tin* src = in + (row0 + r) * ld_in;
 #pragma unroll
-      for (int e = 0; e < 8; ++e) f[j][e] = 0.f;
+    for (int j = 0; j < CPL; ++j) {
+      const int c = lane + 32 * j;
+      if (c < chunks_in && row0 + r < n) load8_stream(src, c, dim, vec_ok, f[r][j]);
+      else {
+#pragma unroll
+        for (int e = 0; e < 8; ++e) f[r][j][e] = 0.f;
+      }
     }
   }
-  float ss = 0.f;
+  float ss[R];
 #pragma unroll
-  for (int j = 0; j < CPL; ++j) {
-    if (lane + 32 * j < chunks_in) {
+  for (int r = 0; r < R; ++r) {
+    ss[r] = 0.f;
 #pragma unroll
-      for (int e = 0; e < 8; ++e) ss = fmaf(f[j][e], f[j][e], ss);
+    for (int j = 0; j < CPL; ++j) {
+      if (lane + 32 * j < chunks_in) {
+#pragma unroll
+        for (int e = 0; e < 8; ++e) ss[r] = fmaf(f[r][j][e], f[r][j][e], ss[r]);
+      }
     }
   }
-  ss = warp_sum(ss);
-  const float nrm = sqrtf(ss);
 #pragma unroll
-  for (int j = 0; j < CPL; ++j) {
-    const int c = lane + 32 * j;
-    if (c < chunks_out) {
+  for (int r = 0; r < R; ++r) ss[r] = warp_sum(ss[r]);
 #pragma unroll
-      for (int e = 0; e < 8; ++e) f[j][e] = nrm > 0.f ? __fdiv_rn(f[j][e], nrm) : 0.f;
-      store8(dst, c, f[j]);
+  for (int r = 0; r < R; ++r) {
+    if (row0 + r >= n) break;
+    const float nrm = sqrtf(ss[r]);
+    Tout* dst = out + (row0 + r) * ld_out;
+#pragma unroll
+    for (int j = 0; j < CPL; ++j) {
+      const int c = lane + 32 * j;
+      if (c < chunks_out) {
+#pragma unroll
+        for (int e = 0; e < 8; ++e) f[r][j][e] = nrm > 0.f ? __fdiv_rn(f[r][j][e], nrm) : 0.f;
+        store8(dst, c, f[r][j]);
+      }
     }
+    if (lane == 0 && norms) norms[row0 + r] = nrm;
   }
-  if (lane == 0 && norms) norms[row] = nrm;
 }
 
 // ---- K1 -------------------------------------------------------------------

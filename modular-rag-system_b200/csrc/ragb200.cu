@@ -268,16 +268,17 @@ template <typename Tin, typename Tout>
 static int norm_pack_launch(const void* in, int64_t n, int dim, int64_t ld_in, void* out, int64_t ld_out,
                             float* norms, cudaStream_t st) {
   const bool vec_ok = ((uintptr_t)in % 16 == 0) && ((ld_in * sizeof(Tin)) % 16 == 0);
-  const int rows_per_cta = 8;
-  const int64_t grid = (n + rows_per_cta - 1) / rows_per_cta;
   const int64_t chunks = std::max<int64_t>((dim + 7) / 8, ld_out / 8);
   static const bool generic_only = getenv("RAGB_NORM_PACK_GENERIC") != nullptr;  // A/B runs
 #define NP_ARGS (const Tin*)in, n, dim, ld_in, (Tout*)out, ld_out, norms, vec_ok
-  if (generic_only || chunks > 128) norm_pack_kernel<Tin, Tout><<<(unsigned)grid, 256, 0, st>>>(NP_ARGS);
-  else if (chunks <= 32) norm_pack_reg_kernel<Tin, Tout, 1><<<(unsigned)grid, 256, 0, st>>>(NP_ARGS);
-  else if (chunks <= 64) norm_pack_reg_kernel<Tin, Tout, 2><<<(unsigned)grid, 256, 0, st>>>(NP_ARGS);
-  else if (chunks <= 96) norm_pack_reg_kernel<Tin, Tout, 3><<<(unsigned)grid, 256, 0, st>>>(NP_ARGS);
-  else norm_pack_reg_kernel<Tin, Tout, 4><<<(unsigned)grid, 256, 0, st>>>(NP_ARGS);
+  // rows per warp: 4 / 2 (16-bit / fp32 input) up to 512 elements, 2 / 1 up to 1024
+  constexpr int RS = sizeof(Tin) == 2 ? 4 : 2, RL = sizeof(Tin) == 2 ? 2 : 1;
+  auto grid_for = [&](int rows_per_warp) { return (unsigned)((n + 8 * rows_per_warp - 1) / (8 * rows_per_warp)); };
+  if (generic_only || chunks > 128) norm_pack_kernel<Tin, Tout><<<grid_for(1), 256, 0, st>>>(NP_ARGS);
+  else if (chunks <= 32) norm_pack_reg_kernel<Tin, Tout, 1, RS><<<grid_for(RS), 256, 0, st>>>(NP_ARGS);
+  else if (chunks <= 64) norm_pack_reg_kernel<Tin, Tout, 2, RS><<<grid_for(RS), 256, 0, st>>>(NP_ARGS);
+  else if (chunks <= 96) norm_pack_reg_kernel<Tin, Tout, 3, RL><<<grid_for(RL), 256, 0, st>>>(NP_ARGS);
+  else norm_pack_reg_kernel<Tin, Tout, 4, RL><<<grid_for(RL), 256, 0, st>>>(NP_ARGS);
 #undef NP_ARGS
   LAUNCHED();
   return RAGB_OK;
@@ -788,16 +789,23 @@ static int gemm_pair_launch(ragb_store* s, const float* q, int64_t nq, int k, in
   // kpad <= 32: candidate buffers in shared memory, 5-stage ring; kpad 64 / 128: buffers in global memory, 6 stages
   const int E = kpad <= 32 ? 2 : kpad == 64 ? 4 : 8;
   if (kpad > 128) return RAGB_EUNSUPPORTED;
-  const int n_stages = E == 2 ? kPairStagesSmall : kPairStagesLarge;
-  const size_t smem = 1024 + (size_t)n_stages * kPairStageBytes + (E == 2 ? (size_t)kGemmM * (kPairCapSmall + 1) * 8 : 0) +
-                      (2 * n_stages + 4) * 8 + 16;
+  // dim <= 384: the query tile stays in shared memory, the ring carries corpus k-blocks only (gemm_pair.cuh: kQRes)
+  const bool qres = n_kb <= kPairQResMaxKB && env_int("RAGB_PAIR_QRES", 1);
+  const int n_stages = qres ? (E == 2 ? kPairStagesSmallQ : kPairStagesLargeQ) : (E == 2 ? kPairStagesSmall : kPairStagesLarge);
+  const size_t cand_stride = E == 2 ? (qres ? kPairCapSmallQ : kPairCapSmall) + 1 : 32 * E;
+  const size_t smem = 1024 + (qres ? (size_t)n_kb * kStageBytesA + (size_t)n_stages * kStageBytesA : (size_t)n_stages * kPairStageBytes) +
+                      (E == 2 ? (size_t)kGemmM * cand_stride * 8 : 0) + (2 * n_stages + 5) * 8 + 16;
   typedef void (*PairKernel)(const CUtensorMap, const CUtensorMap, const TsParams);
-  PairKernel kern = E == 2 ? gemm_topk_pair_kernel<2, kPairStagesSmall>
-                  : E == 4 ? gemm_topk_pair_kernel<4, kPairStagesLarge> : gemm_topk_pair_kernel<8, kPairStagesLarge>;
-  const int ei = E == 2 ? 0 : E == 4 ? 1 : 2;
-  static bool attr_set[3] = {false, false, false};
+  PairKernel kern = qres ? (E == 2 ? gemm_topk_pair_kernel<2, kPairStagesSmallQ, true>
+                          : E == 4 ? gemm_topk_pair_kernel<4, kPairStagesLargeQ, true> : gemm_topk_pair_kernel<8, kPairStagesLargeQ, true>)
+                         : (E == 2 ? gemm_topk_pair_kernel<2, kPairStagesSmall>
+                          : E == 4 ? gemm_topk_pair_kernel<4, kPairStagesLarge> : gemm_topk_pair_kernel<8, kPairStagesLarge>);
+  const int ei = (E == 2 ? 0 : E == 4 ? 1 : 2) + (qres ? 3 : 0);
+  static bool attr_set[6] = {false, false, false, false, false, false};
   if (!attr_set[ei]) {
-    CU_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    // the resident-query variants are sized by dim: allow the largest (6 k-blocks) once
+    const size_t smem_max = smem + (qres ? (size_t)(kPairQResMaxKB - n_kb) * kStageBytesA : 0);
+    CU_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_max));
     attr_set[ei] = true;
   }
   cudaLaunchConfig_t cfg = {};

@@ -31,4 +31,4 @@ tot = sum(b[0] for b in body) or 1.0
 toti = sum(b[1] for b in body) or 1.0
 print(f"total samples {tot:.0f}, instructions {toti:.0f}")
 for v, ins, r in sorted(body, key=lambda b: -b[0])[:n]:
-    print(f"{100 * v / tot:6.2f}% stall {100 * ins / toti:6.2f}% inst  {r[0][:18]:18s} {r[srci][:140]}")
+    print(f"{100 * v / tot:6.2f}% stall {100 * ins / toti:6.2f}% inst  {r[0][:18]:18s} {(r[srci].strip() or (r[3].strip() if len(r) > 3 else ""))[:140]}")
