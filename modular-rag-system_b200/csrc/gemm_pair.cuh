@@ -186,7 +186,19 @@ __device__ __forceinline__ uint64_t warp_prune(uint64_t* base, int n, int k, int
 // chunk in fp32 and keeps the k best rows; row range, valid mask and the user threshold are
 // applied there, exactly.  Here rows outside the range / masked out are only kept from raising a
 // chunk's maximum (kMasked), so the threshold stays a lower bound.
+// Shared running threshold (p.gthr): the row splits of one query each see 1/n_splits of the rows, so each split's own
+// k-th best chunk maximum tightens n_splits times more slowly than it could.  Any split's k-th best chunk maximum is
+// a lower bound of the query's k-th best over ALL rows, so it may cut every other split as well: after each prune a
+// lane publishes its threshold with atomicMax (order-preserving bits, 0 = none yet) and every thread picks up the
+// query's word once per tile (the load is issued before the wait for the accumulator).  Which chunks a split keeps
+// then depends on timing; the k best chunks overall — all the finish kernel uses — do not.
+__device__ __forceinline__ unsigned ld_relaxed_u32(const unsigned* ptr) {
+  unsigned v;
+  asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(ptr) : "memory");
+  return v;
+}
 struct EpiCtx {
+  unsigned* gthr;       // this query's word of the shared threshold, or null
   uint64_t* my;         // this query's candidate buffer
   uint64_t* warp_cand;  // buffer of lane 0 of this warp; lane j's is warp_cand + j*stride
   int cnt;
@@ -240,7 +252,10 @@ __device__ __forceinline__ void epi_prune(EpiCtx& e, const TsParams& p, int lane
     const uint64_t kth = warp_prune<E>(e.warp_cand + (size_t)j * kStride, n, p.k, lane, &keep);
     if (lane == j) {
       e.cnt = keep;
-      if (n >= p.k) e.fthr = fmaxf(e.user_fast, fast_bound(key_score(kth), p.flags));
+      if (n >= p.k) {
+        e.fthr = fmaxf(e.fthr, fmaxf(e.user_fast, fast_bound(key_score(kth), p.flags)));
+        if (e.gthr) atomicMax(e.gthr, order_bits(e.fthr));
+      }
     }
     __syncwarp();
   }
@@ -399,6 +414,7 @@ gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_co
     e.my = cand + (size_t)tid * Cand::stride;
     e.warp_cand = cand + (size_t)(quarter * 32) * Cand::stride;
     e.cnt = 0;
+    e.gthr = p.gthr ? p.gthr + (size_t)qt * kGemmM + tid : nullptr;
     // rows of the query tile past nq are zero padding: they must never take the candidate path
     // the 16-bit-query scores only SELECT: the user threshold is applied with slack here, exactly by the re-score
     e.user_fast = ((int64_t)qt * kGemmM + tid < p.nq) ? fast_bound(p.threshold - p.sel_slack, p.flags) : INFINITY;
@@ -406,8 +422,10 @@ gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_co
     uint32_t acc = 0, aph = 0;
     for (int64_t t = t0; t < t1; ++t) {
       const int64_t row0 = p.row_begin + t * kPairN;
+      const unsigned gv = e.gthr ? ld_relaxed_u32(e.gthr) : 0u;
       mbar_wait(&tfull_bar[acc], aph);
       tc_fence_after();
+      if (gv) e.fthr = fmaxf(e.fthr, unorder_bits(gv));
       const uint32_t taddr = lane_base + acc * (uint32_t)kPairN;
       // two register sets: the TMEM load of the next 32 columns is in flight while this one is examined
       uint32_t ra[32], rb[32];

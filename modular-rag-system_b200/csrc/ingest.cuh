@@ -99,8 +99,8 @@ __global__ void __launch_bounds__(256) norm_pack_kernel(const Tin* __restrict__ 
 
 // K2, rows of at most 256*CPL elements: a warp takes R consecutive rows, fetches each ONCE (streaming 128-bit loads,
 // all R*CPL of a lane issued before the first is used) and keeps them in registers between the sum of squares and
-// the divide.  R is chosen by the host so that a lane has 64-128 bytes in flight (16-bit rows of 384 elements are
-// only 768 bytes: one row per warp left HBM at half rate).  Same summation order per row as the generic kernel
+// the divide.  R is chosen by the host (1 today: more rows per warp cost more in occupancy than the extra bytes in
+// flight return, see norm_pack_launch).  Same summation order per row as the generic kernel
 // above (lane-serial over its chunks, then the shuffle tree), so both produce the same bits.
 template <typename Tin, typename Tout, int CPL, int R>
 __global__ void __launch_bounds__(256) norm_pack_reg_kernel(const Tin* __restrict__ in, int64_t n, int dim,

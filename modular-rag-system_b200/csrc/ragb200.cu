@@ -271,8 +271,9 @@ static int norm_pack_launch(const void* in, int64_t n, int dim, int64_t ld_in, v
   const int64_t chunks = std::max<int64_t>((dim + 7) / 8, ld_out / 8);
   static const bool generic_only = getenv("RAGB_NORM_PACK_GENERIC") != nullptr;  // A/B runs
 #define NP_ARGS (const Tin*)in, n, dim, ld_in, (Tout*)out, ld_out, norms, vec_ok
-  // rows per warp: 4 / 2 (16-bit / fp32 input) up to 512 elements, 2 / 1 up to 1024
-  constexpr int RS = sizeof(Tin) == 2 ? 4 : 2, RL = sizeof(Tin) == 2 ? 2 : 1;
+  // measured on B200 (fp32 -> fp16, 2M x 384): R=1 5.50 TB/s, R=2 5.26; fp16 -> fp16: R=1 3.35, R=4 1.52 (128 registers,
+  // 2 CTAs per SM) — occupancy beats bytes in flight per lane here, so one row per warp
+  constexpr int RS = 1, RL = 1;
   auto grid_for = [&](int rows_per_warp) { return (unsigned)((n + 8 * rows_per_warp - 1) / (8 * rows_per_warp)); };
   if (generic_only || chunks > 128) norm_pack_kernel<Tin, Tout><<<grid_for(1), 256, 0, st>>>(NP_ARGS);
   else if (chunks <= 32) norm_pack_reg_kernel<Tin, Tout, 1, RS><<<grid_for(RS), 256, 0, st>>>(NP_ARGS);
@@ -846,9 +847,15 @@ static int gemm_pair_launch(ragb_store* s, const float* q, int64_t nq, int k, in
   }
   const size_t part_bytes = (size_t)nq_pad * splits * kpad * sizeof(uint64_t);
   const size_t cand_bytes = E == 2 ? 0 : (size_t)n_qt * splits * kGemmM * (32 * E) * sizeof(uint64_t);
-  RB_TRY(grow(&s->ws, &s->ws_bytes, part_bytes + cand_bytes, false));
+  const size_t gthr_bytes = (splits > 1 && env_int("RAGB_PAIR_GTHR", 1)) ? (size_t)nq_pad * sizeof(unsigned) : 0;
+  RB_TRY(grow(&s->ws, &s->ws_bytes, part_bytes + cand_bytes + gthr_bytes, false));
   p.out = (uint64_t*)s->ws;
   p.cand_ws = E == 2 ? nullptr : (uint64_t*)((char*)s->ws + part_bytes);
+  p.gthr = nullptr;
+  if (gthr_bytes) {  // the row splits of a query share their running threshold (gemm_pair.cuh)
+    p.gthr = (unsigned*)((char*)s->ws + part_bytes + cand_bytes);
+    CU_TRY(cudaMemsetAsync(p.gthr, 0, gthr_bytes, st));
+  }
   cfg.gridDim = dim3((unsigned)(n_qt * splits));
   {
     ProfScope prof(s, st);
