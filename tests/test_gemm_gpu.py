@@ -225,3 +225,33 @@ def test_single_tile_batches_on_both_kernels(nq, k, monkeypatch):
     monkeypatch.delenv("RAGB_PAIR_SMALL")
     ids, sc = s.search(Q, k, "cosine")           # default routing
     _check(ids, sc, X, Q, k, "cosine", -np.inf, False, TOL["fp16"])
+
+
+@pytest.mark.parametrize("dim,nq,k", [(384, 300, 10), (256, 700, 100), (320, 130, 32), (100, 260, 64)])
+def test_resident_query_tile_and_shared_threshold_switches(dim, nq, k, monkeypatch):
+    """dim <= 384 keeps the query tile in shared memory (kQRes) and the row splits of a query share one running
+    threshold (gthr) — csrc/gemm_pair.cuh.  Neither may change what is returned: every combination of the two A/B
+    switches must agree with the oracle and with each other, exact ties (duplicated rows) included."""
+    FORCE_GEMM, _, _ = _flags()
+    rng = np.random.default_rng(dim * 7 + nq + k)
+    n = 60000
+    X = rng.standard_normal((n, dim)).astype(np.float32)
+    X[50000:50040] = X[123]                      # 41 copies of one row: ties across chunks and across row splits
+    Q = rng.standard_normal((nq, dim)).astype(np.float32)
+    Q[0] = X[123] + 0.05 * rng.standard_normal(dim).astype(np.float32)
+    for i in range(5, nq, 11):
+        Q[i] = X[(i * 977) % n] + 0.3 * rng.standard_normal(dim).astype(np.float32)
+    s = _store(X, "fp16")
+    got = []
+    for qres, gthr in (("1", "1"), ("0", "1"), ("1", "0"), ("0", "0")):
+        monkeypatch.setenv("RAGB_PAIR_QRES", qres)
+        monkeypatch.setenv("RAGB_PAIR_GTHR", gthr)
+        ids, sc = s.search(Q, k, "cosine", flags=FORCE_GEMM)
+        _check(ids, sc, X, Q, k, "cosine", -np.inf, False, TOL["fp16"])
+        got.append((np.array(ids), np.array(sc)))
+    for ids, sc in got[1:]:
+        np.testing.assert_array_equal(ids, got[0][0])   # the fp32 re-score decides: same rows, same order
+        np.testing.assert_array_equal(sc, got[0][1])
+    top = set(int(x) for x in got[0][0][0][:min(k, 41)])
+    assert top <= ({123} | set(range(50000, 50040)))
+    s.close()
