@@ -11,9 +11,10 @@ cur = None
 for r in rows[hdr + 1:]:
     if len(r) < len(h):
         continue
-    if r[0].strip().isdigit():
-        cur = int(r[0])
-    if lo is not None and (cur is None or not (lo <= cur <= hi)):
+    if not r[0].strip().isdigit():
+        continue  # SASS rows repeat what their CUDA source line row already aggregates
+    cur = int(r[0])
+    if lo is not None and not (lo <= cur <= hi):
         continue
     for i, c in cols:
         try:
