@@ -852,6 +852,7 @@ static int gemm_pair_launch(ragb_store* s, const float* q, int64_t nq, int k, in
   p.out = (uint64_t*)s->ws;
   p.cand_ws = E == 2 ? nullptr : (uint64_t*)((char*)s->ws + part_bytes);
   p.gthr = nullptr;
+  p.full_sort = env_int("RAGB_PAIR_FULLSORT", 0);
   if (gthr_bytes) {  // the row splits of a query share their running threshold (gemm_pair.cuh)
     p.gthr = (unsigned*)((char*)s->ws + part_bytes + cand_bytes);
     CU_TRY(cudaMemsetAsync(p.gthr, 0, gthr_bytes, st));
