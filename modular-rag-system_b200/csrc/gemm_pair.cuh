@@ -174,6 +174,27 @@ __device__ __forceinline__ void warp_merge_desc(uint64_t (&v)[E], int lane) {
   }
 }
 
+// A buffer of 32*E slots whose lower half (16*E keys) is sorted descending and whose upper half holds n - 16*E new
+// keys in any order -> lo = the 16*E best of all of them, descending: sort only the new half, take the larger of
+// lower[i] and upper[last - i] (the best half of the union, as a bitonic sequence), merge.
+template <int E>
+__device__ __forceinline__ void warp_best_half(const uint64_t* base, int n, int lane, uint64_t (&lo)[E / 2]) {
+  constexpr int H = E / 2;
+  uint64_t hi[H];
+#pragma unroll
+  for (int e = 0; e < H; ++e) {
+    lo[e] = base[e * 32 + lane];
+    hi[e] = ((e + H) * 32 + lane < n) ? base[(e + H) * 32 + lane] : 0ull;
+  }
+  warp_sort_desc<H>(hi, lane);
+#pragma unroll
+  for (int e = 0; e < H; ++e) {
+    const uint64_t o = __shfl_sync(0xffffffffu, hi[H - 1 - e], 31 - lane);
+    lo[e] = lo[e] > o ? lo[e] : o;
+  }
+  warp_merge_desc<H>(lo, lane);
+}
+
 // All 32 lanes: sort the n keys of one query's buffer, keep the best min(n,k) in place (sorted),
 // return the k-th best (0 if fewer than k are held).  `sorted` = how many keys at the front of the buffer are still
 // in descending order from the previous prune (the epilogue only appends behind them).
@@ -187,19 +208,8 @@ __device__ __forceinline__ uint64_t warp_prune(uint64_t* base, int n, int k, int
     // and merge.  Half the compare-exchanges of the full sort (E=8: 144 against 288 per lane).
     if (sorted == 16 * E && k == 16 * E) {
       constexpr int H = E / 2;
-      uint64_t lo[H], hi[H];
-#pragma unroll
-      for (int e = 0; e < H; ++e) {
-        lo[e] = base[e * 32 + lane];
-        hi[e] = ((e + H) * 32 + lane < n) ? base[(e + H) * 32 + lane] : 0ull;
-      }
-      warp_sort_desc<H>(hi, lane);
-#pragma unroll
-      for (int e = 0; e < H; ++e) {
-        const uint64_t o = __shfl_sync(0xffffffffu, hi[H - 1 - e], 31 - lane);
-        lo[e] = lo[e] > o ? lo[e] : o;
-      }
-      warp_merge_desc<H>(lo, lane);
+      uint64_t lo[H];
+      warp_best_half<E>(base, n, lane, lo);
       __syncwarp();
 #pragma unroll
       for (int e = 0; e < H; ++e) base[e * 32 + lane] = lo[e];
@@ -329,12 +339,20 @@ __device__ __forceinline__ void epi_flush(EpiCtx& e, int64_t qrow0, int split, c
       const uint64_t v = warp_top32_of_64(base, n, lane);
       if (lane < p.kpad) out[lane] = lane < keep ? v : 0ull;
     } else {
-      uint64_t v[E];
+      const int sorted = p.full_sort ? 0 : __shfl_sync(0xffffffffu, e.sorted, j);
+      if (sorted == 16 * E && p.k == 16 * E) {  // as in warp_prune: the lower half is in order, keep == k == 16*E
+        uint64_t lo[E / 2];
+        warp_best_half<E>(base, n, lane, lo);
 #pragma unroll
-      for (int x = 0; x < E; ++x) v[x] = (x * 32 + lane < n) ? base[x * 32 + lane] : 0ull;
-      warp_sort_desc<E>(v, lane);
+        for (int x = 0; x < E / 2; ++x) out[x * 32 + lane] = lo[x];
+      } else {
+        uint64_t v[E];
 #pragma unroll
-      for (int x = 0; x < E / 2; ++x) out[x * 32 + lane] = (x * 32 + lane < keep) ? v[x] : 0ull;
+        for (int x = 0; x < E; ++x) v[x] = (x * 32 + lane < n) ? base[x * 32 + lane] : 0ull;
+        warp_sort_desc<E>(v, lane);
+#pragma unroll
+        for (int x = 0; x < E / 2; ++x) out[x * 32 + lane] = (x * 32 + lane < keep) ? v[x] : 0ull;
+      }
     }
   }
 }
