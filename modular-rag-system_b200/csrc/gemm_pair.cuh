@@ -93,10 +93,14 @@ template <int E, bool Q = false> struct CandCfg {
 constexpr int kPairQResMaxKB = 6;
 constexpr int kPairStagesSmallQ = 5;   // x 16 KB, next to 96 KB of queries and the 49 KB of candidate buffers
 constexpr int kPairStagesLargeQ = 8;   // x 16 KB, next to 96 KB of queries
-// rows behind one candidate key.  k <= 32 (E == 2): 16 — half of one tcgen05.ld of 32 columns; the finish kernel then
-// re-reads half as many rows (1M x 384, B=1024: 133 -> 96 us).  k > 32: 32 — twice the chunks would double the
-// inserts into the global-memory buffers, which costs more than the finish kernel saves (1M x 384 top-100: +8 %).
-template <int E> struct ChunkCfg { static constexpr int rows = E == 2 ? 16 : 32; };
+// rows behind one candidate key: 16 — half of one tcgen05.ld of 32 columns; the finish kernel then re-reads half as
+// many rows (1M x 384, B=1024, top-10: 133 -> 96 us).  For k > 32 this used to lose (twice the inserts into the
+// global-memory buffers, +8 % at 1M x 384 top-100 with the full-sort prune); with the sorted-prefix prune it wins or
+// ties: 1M x 384 top-100 B=1024 1.96 -> 1.77 ms, 10M x 768 13.7 -> 13.4 ms, 12.5M x 384 B=4096 33.4 -> 33.6 ms.
+#ifndef RAGB_CHUNK_ROWS_LARGE
+#define RAGB_CHUNK_ROWS_LARGE 16  // build-time A/B: -DRAGB_CHUNK_ROWS_LARGE=32
+#endif
+template <int E> struct ChunkCfg { static constexpr int rows = E == 2 ? 16 : RAGB_CHUNK_ROWS_LARGE; };
 
 __device__ __forceinline__ float fmax3(float a, float b, float c) {
   float r;

@@ -705,8 +705,9 @@ static int gemm_finish_chunks(ragb_store* s, const float* q, int64_t nq, int k, 
   if (smem > 200 * 1024) return fail(RAGB_EUNSUPPORTED, "internal: %d splits x kpad %d do not fit the finish kernel", splits, kpad);
   // rows per chunk must match the epilogue that produced the keys (gemm_pair.cuh: ChunkCfg)
   typedef void (*FinishKernel)(const FinishParams);
-  const bool small = kpad <= 32;
-  static_assert(ChunkCfg<2>::rows == 16 && ChunkCfg<4>::rows == 32 && ChunkCfg<8>::rows == 32, "finish kernel variants");
+  const bool small = kpad <= 32 || ChunkCfg<8>::rows == 16;
+  static_assert(ChunkCfg<2>::rows == 16 && ChunkCfg<4>::rows == ChunkCfg<8>::rows && (ChunkCfg<8>::rows == 32 || ChunkCfg<8>::rows == 16),
+                "finish kernel variants");
   FinishKernel kern = s->dtype == RAGB_BF16 ? (small ? finish_chunks_kernel<__nv_bfloat16, 16> : finish_chunks_kernel<__nv_bfloat16, 32>)
                                             : (small ? finish_chunks_kernel<__half, 16> : finish_chunks_kernel<__half, 32>);
   if (smem > 48 * 1024) CU_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
