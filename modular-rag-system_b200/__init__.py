@@ -9,8 +9,8 @@ from ._lib import RagbError, build, lib  # noqa: F401
 from .store import DeviceStore, gather_merge_dev, kpad_of, launch_count, merge_keys_dev, pool_norm_pack_dev  # noqa: F401
 from .sharded import PeerBuffers, ShardedSearcher, shard_bounds  # noqa: F401
 from .embedder import PooledEmbedder, PooledEmbeddingGenerator  # noqa: F401
-from .rag_store import B200VectorStore, RAGDocument, RAGQuery, RAGResult, install  # noqa: F401
+from .rag_store import B200VectorStore, RAGDocument, RAGQuery, RAGResult, install, uninstall  # noqa: F401
 
 __all__ = ["DeviceStore", "RagbError", "build", "lib", "kpad_of", "launch_count", "merge_keys_dev",
-           "ShardedSearcher", "PeerBuffers", "gather_merge_dev", "shard_bounds", "B200VectorStore", "RAGDocument", "RAGQuery", "RAGResult", "install",
+           "ShardedSearcher", "PeerBuffers", "gather_merge_dev", "shard_bounds", "B200VectorStore", "RAGDocument", "RAGQuery", "RAGResult", "install", "uninstall",
            "PooledEmbedder", "PooledEmbeddingGenerator", "pool_norm_pack_dev"]

@@ -21,6 +21,10 @@ Parity status
   ``embedding_pipeline.py:424`` and ``ollama_rag_system.py:163``).  The
   restatement follows that library's published ``Pooling(mean)`` +
   ``Normalize`` modules.
+* ``oracle/_ref/``             : the UNMODIFIED reference modules (git-ignored;
+  ``oracle/fetch_ref.py`` copies them from ``/root/reference`` and refuses a
+  file whose SHA-256 is not the surveyed commit's).  ``ref_path()`` gives the
+  directory to the drop-in tests and to bench.py's literal CPU baseline.
 """
 
 from .ref_search import (  # noqa: F401
@@ -36,3 +40,10 @@ from .ref_ingest import (  # noqa: F401
     pack_bf16,
     unpack_bf16,
 )
+
+
+def ref_path():
+    """Directory holding the unmodified reference modules (oracle/_ref, see fetch_ref.py), or None when the copy is
+    absent or not bit-identical to the surveyed reference."""
+    from . import fetch_ref
+    return str(fetch_ref.OUT) if fetch_ref.verify() else None

@@ -128,72 +128,7 @@ def test_batched_policy_flags():
     assert (ids == np.array([4999, 4998, 4997])).all() and (sc == 0).all()
 
 
-def test_full_size_properties():
-    """BASELINE config 2 shape (1M x 384 fp16, top-10, batch 1024): planted rows come back first,
-    scores are sorted, and the batched result agrees with the scan on a sample of queries."""
-    import torch
-    from modular_rag_system_b200 import DeviceStore
-    from modular_rag_system_b200._lib import FORCE_SCAN
-    n, d, nq, k = 1_000_000, 384, 1024, 10
-    g = torch.Generator(device="cuda").manual_seed(0)
-    s = DeviceStore(d, "fp16", n)
-    for r0 in range(0, n, 250_000):
-        s.add_dev(torch.randn((250_000, d), generator=g, device="cuda"))
-    Q = torch.randn((nq, d), generator=g, device="cuda")
-    rows, _ = s.get_rows(123_456, 8)
-    Q[:8] = torch.from_numpy(rows.astype(np.float32)).cuda() + 0.05 * Q[:8]
-    ids, sc = s.search_dev(Q, k, "cosine")
-    torch.cuda.synchronize()
-    ids, sc = ids.cpu().numpy(), sc.cpu().numpy()
-    assert (ids[:8, 0] == 123_456 + np.arange(8)).all()
-    assert (np.diff(sc, axis=1) <= 0).all() and (ids >= 0).all()
-    ids2, sc2 = s.search_dev(Q[:16].contiguous(), k, "cosine", flags=FORCE_SCAN)
-    torch.cuda.synchronize()
-    assert (ids2.cpu().numpy() == ids[:16]).mean() > 0.97
-    assert np.abs(sc2.cpu().numpy() - sc[:16]).max() < 1e-3
-
-
-def _planted_store(n, d, dtype, seed):
-    import torch
-    from modular_rag_system_b200 import DeviceStore
-    g = torch.Generator(device="cuda").manual_seed(seed)
-    s = DeviceStore(d, dtype, n)
-    step = 500_000
-    for r0 in range(0, n, step):
-        s.add_dev(torch.randn((min(step, n - r0), d), generator=g, device="cuda"))
-    return s, g
-
-
-@pytest.mark.parametrize("n,d,dtype,nq,k", [
-    (10_000_000, 768, "fp16", 1024, 10),    # BASELINE configs[3] / north_star target shape on one GPU
-    (12_500_000, 384, "bf16", 4096, 100),   # one GPU's share of configs[4] (100M x 384 bf16, top-100, batch 4096)
-])
-def test_full_size_properties_headline_shapes(n, d, dtype, nq, k):
-    """At BASELINE.json's full sizes the oracle cannot run; size-independent properties instead: planted rows come
-    back first, scores are sorted, ids are unique and in range, and the tensor-core result equals the
-    bandwidth-bound scan (a different kernel, fp32 queries) on a sample of the queries."""
-    import torch
-    from modular_rag_system_b200._lib import FORCE_SCAN
-    s, g = _planted_store(n, d, dtype, 3)
-    Q = torch.randn((nq, d), generator=g, device="cuda")
-    planted = [7, n // 3, n - 9]
-    for j, r in enumerate(planted):
-        rows, _ = s.get_rows(r, 1)
-        x = rows.astype(np.float32) if dtype == "fp16" else (rows.astype(np.uint32) << 16).view(np.float32)
-        Q[j] = torch.from_numpy(x[0]).cuda() + 0.05 * Q[j]
-    ids, sc = s.search_dev(Q, k, "cosine")
-    torch.cuda.synchronize()
-    ids, sc = ids.cpu().numpy(), sc.cpu().numpy()
-    assert [int(ids[j, 0]) for j in range(3)] == planted
-    assert (np.diff(sc, axis=1) <= 0).all() and (ids >= 0).all() and (ids < n).all()
-    assert all(len(set(row.tolist())) == k for row in ids[:64])
-    sample = Q[:3].contiguous()
-    ids2, sc2 = s.search_dev(sample, k, "cosine", flags=FORCE_SCAN)
-    torch.cuda.synchronize()
-    tol = 1e-3 if dtype == "fp16" else 4e-3
-    assert (ids2.cpu().numpy() == ids[:3]).mean() > 0.95
-    assert np.abs(sc2.cpu().numpy() - sc[:3]).max() < tol
-    s.close()
+# full-size (1M x 384, 10M x 768, 12.5M x 384) parity against the float64 oracle: tests/test_fullsize_parity_gpu.py
 
 
 @pytest.mark.parametrize("nq,k", [(4, 10), (17, 5), (128, 32), (40, 100), (2, 64)])

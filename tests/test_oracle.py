@@ -79,3 +79,53 @@ def test_pack_bf16_roundtrip():
     import torch
     t = torch.from_numpy(x).bfloat16().view(torch.int16).numpy().view(np.uint16)
     assert (t == b).all()
+
+
+class _HostStore:
+    """numpy stand-in for DeviceStore.get_rows (the only thing oracle/parity.py asks of a store)."""
+
+    def __init__(self, X16, dtype):
+        self.X, self.dtype = X16, dtype
+
+    def __len__(self):
+        return len(self.X)
+
+    def get_rows(self, r0, n):
+        return self.X[r0:r0 + n], None
+
+
+@pytest.mark.parametrize("dtype", ["fp16", "bf16"])
+def test_full_size_parity_helper_equals_plain_oracle(dtype):
+    """oracle/parity.py (slabbed, threaded, fed from packed rows) returns what search_f64 returns on the same rows, and
+    its judge accepts the oracle's own answer / rejects a corrupted one."""
+    from oracle import parity
+    rng = np.random.default_rng(7)
+    X = rng.standard_normal((5000, 96)).astype(np.float32)
+    X /= np.linalg.norm(X, axis=1, keepdims=True)
+    X[4000] = X[10]                                   # exact tie across slabs: newer row first
+    packed = X.astype(np.float16) if dtype == "fp16" else ref_ingest.pack_bf16(X)
+    Xp = packed.astype(np.float64) if dtype == "fp16" else ref_ingest.unpack_bf16(packed).astype(np.float64)
+    Q = rng.standard_normal((6, 96)).astype(np.float32)
+    Q[0] = X[10]
+    store = _HostStore(packed, dtype)
+    for metric in ("ip", "cosine"):
+        ids, sc = ref_search.search_f64(Xp, Q, 7, metric)
+        oi, osc, tables = parity.oracle_topk(store, Q, 7, metric, score_rows=list(ids), slab_rows=777, threads=3)
+        np.testing.assert_array_equal(oi, ids)
+        np.testing.assert_allclose(osc, sc, rtol=0, atol=1e-12)
+        assert oi[0][:2].tolist() == [4000, 10]
+        res = parity.judge(ids, sc.astype(np.float32), oi, osc, tables, 1e-3)
+        assert res["check_topk_failures"] == 0 and res["recall_at_k"] == 1.0 and res["recall_at_k_strict"] == 1.0
+        assert res["max_abs_score_err"] < 1e-6
+    bad = ids.copy()
+    bad[2, 0] = 1234                                   # a row that is nowhere near the top
+    _, _, tables = parity.oracle_topk(store, Q, 7, "cosine", score_rows=list(bad), slab_rows=2048)
+    res = parity.judge(bad, sc.astype(np.float32), oi, osc, tables, 1e-3)
+    assert res["check_topk_failures"] == 1 and res["recall_at_k_strict"] < 1.0
+    full = parity.check_store(store, Q, ids, sc.astype(np.float32), 7, "cosine", 1e-3, np.array([0, 3, 5]),
+                              extra={"again": (ids[[0, 3, 5]], sc[[0, 3, 5]].astype(np.float32))})
+    assert full["parity_queries"] == 3 and full["extra"]["again"]["check_topk_failures"] == 0
+    s1 = np.sort(rng.random((40, 8)).astype(np.float32), axis=1)[:, ::-1].copy()
+    s1[13, 6] = s1[13, 7]                              # smallest k / k+1 gap
+    pick = parity.sample_queries(s1, 7, 10, always=[39])
+    assert 39 in pick and 13 in pick and len(pick) == 10

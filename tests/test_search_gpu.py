@@ -7,7 +7,7 @@ from helpers import SEARCH_FIXTURES, load, policy_valid
 
 pytestmark = pytest.mark.gpu
 
-TOL = {"fp16": 1e-3, "bf16": 8e-3, "fp32": 2e-5}  # |score - float64 oracle|; 1e-3 is north_star's bar for fp16
+TOL = {"fp16": 1e-3, "bf16": 4e-3, "fp32": 2e-5}  # |score - float64 oracle|; 1e-3 is north_star's bar for fp16, 4e-3 = DESIGN.md §4
 
 
 def _store(X, dtype):
