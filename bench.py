@@ -37,6 +37,9 @@ WORKLOADS = {
     "10Mx768": dict(n=10_000_000, d=768, dtype="fp16"),
     # BASELINE.json configs[1]
     "1Mx384": dict(n=1_000_000, d=384, dtype="fp16"),
+    # the two other cells of BASELINE.json's metric ("1M/10M x 384/768")
+    "1Mx768": dict(n=1_000_000, d=768, dtype="fp16"),
+    "10Mx384": dict(n=10_000_000, d=384, dtype="fp16"),
     # BASELINE.json configs[4]: run with --k 100 --batch 4096 (--gpus 8: 9.6 GB per GPU; one GPU holds all 76.8 GB too)
     "100Mx384": dict(n=100_000_000, d=384, dtype="bf16"),
 }
@@ -58,6 +61,8 @@ def parse_args():
                     help="N > 1: candidates stored into peer memory by the search kernels (default) or NCCL all-gather")
     ap.add_argument("--no-extras", action="store_true", help="skip the secondary cases (batch 1, 1Mx384)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline leg")
+    ap.add_argument("--no-parity", action="store_true", help="skip the float64-oracle parity check (outside the timed regions)")
+    ap.add_argument("--no-sustained", action="store_true", help="skip the >= 2 s repeat of the headline step")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target CPU time of one baseline sample")
     return ap.parse_args()
 
@@ -76,12 +81,32 @@ def peaks():
 # --------------------------------------------------------------------------- #
 # CPU baseline: the oracle (numpy float64 restatement of ollama_rag_system.py:199-222,480-515)
 # --------------------------------------------------------------------------- #
+def host_cores() -> int:
+    return len(os.sched_getaffinity(0))
+
+
+def pin_blas_threads():
+    """torchrun exports OMP_NUM_THREADS=1 to its workers: the CPU legs would silently run single-threaded at N > 1
+    (round 1: 13.0 queries/s at N=1, 4.5 at N >= 2).  Give the BLAS every core this process may run on, whatever the
+    launcher exported, and report the count.  Returns a context manager; `.threads` is what numpy's BLAS uses inside."""
+    n = host_cores()
+    for v in ("OMP_NUM_THREADS", "OPENBLAS_NUM_THREADS", "MKL_NUM_THREADS"):
+        os.environ[v] = str(n)           # honoured if numpy is not loaded yet
+    from threadpoolctl import threadpool_info, threadpool_limits
+    import numpy  # noqa: F401  (its BLAS must be loaded before the limit is applied)
+    ctx = threadpool_limits(limits=n)    # and this resizes an already-initialised pool
+    got = [i.get("num_threads") for i in threadpool_info() if i.get("user_api") == "blas"]
+    ctx.threads = max(got) if got else n
+    return ctx
+
+
 def cpu_sample(n_total: int, d: int, batch: int, k: int, target_s: float):
     """Time the CPU oracle on a bounded row sample of the same workload; returns
     (qps extrapolated linearly to n_total rows, seconds of the sample, rows in the sample, cores)."""
     import numpy as np
     from oracle import ref_search
-    cores = len(os.sched_getaffinity(0))
+    blas = pin_blas_threads()
+    cores = int(blas.threads)
     rng = np.random.default_rng(0)
     Q = rng.standard_normal((batch, d)).astype(np.float32)
 
@@ -104,6 +129,7 @@ def cpu_sample(n_total: int, d: int, batch: int, k: int, target_s: float):
     X = make(n_s) if n_s != n0 else X0
     t = run(X)
     qps = batch / (t * n_total / n_s)
+    blas.restore_original_limits()
     return qps, t, n_s, cores
 
 
@@ -120,14 +146,69 @@ def literal_rows_per_s(d: int, k: int, n_rows: int = 3000) -> float:
     return n_rows / (time.perf_counter() - t0)
 
 
-def cpu_baseline_obj(wl, batch, k, target_s):
+def literal_ref(d: int, k: int):
+    """The UNMODIFIED reference (oracle/_ref, SHA-256 checked copy of ollama_rag_system.py) timed as shipped:
+    RAGVectorStore.search (:388-525: SQLite fetch, unpickle, per-row float64 cosine, sort) at its own cap of 1000 rows,
+    and its scoring loop (calculate_similarity per row, :199-222 + sorted, :511-515) over 10 000 rows (BASELINE
+    configs[0]).  One core: a pure-Python loop under the GIL.  None when oracle/_ref is absent."""
+    import contextlib
+    import io
+    import numpy as np
+    import oracle
+    path = oracle.ref_path()
+    if path is None:
+        return None
+    sys.path.insert(0, path)
+    try:
+        with contextlib.redirect_stdout(io.StringIO()):
+            import ollama_rag_system as R
+            rng = np.random.default_rng(4)
+            X = rng.standard_normal((10_000, d))
+            q = rng.standard_normal(d)
+            with tempfile.TemporaryDirectory() as td:
+                vs = R.RAGVectorStore(Path(td))
+                with __import__("sqlite3").connect(vs.db_path) as conn:   # bulk insert of the reference's own row format
+                    conn.executemany("INSERT OR REPLACE INTO documents VALUES (?,?,?,?,?,?,?,?)",
+                                     [(f"d{i}", f"chunk {i}", "{}", __import__("pickle").dumps(X[i].tolist()), 1e9 + i, "s", 1.0, 0)
+                                      for i in range(1000)])
+                vs.embedding_generator.embedding_cache["Q"] = q.tolist()
+                qry = R.RAGQuery(query_text="Q", context={}, max_results=k, similarity_threshold=0.0)
+                vs.search(qry)
+                t0 = time.perf_counter()
+                reps = 3
+                for _ in range(reps):
+                    res = vs.search(qry)
+                t_search = (time.perf_counter() - t0) / reps
+                assert res.total_documents_searched == 1000 and len(res.documents) == k
+                gen = vs.embedding_generator
+                rows = [x.tolist() for x in X]
+                ql = q.tolist()
+                t0 = time.perf_counter()
+                sims = [gen.calculate_similarity(ql, r) for r in rows]
+                top = sorted(zip(range(len(rows)), sims), key=lambda t: t[1], reverse=True)[:k]
+                t_loop = time.perf_counter() - t0
+        return {"kind": "_ref", "cores": 1, "unit": "queries/s",
+                "search_n1000": {"value": 1.0 / t_search, "ms_per_query": 1e3 * t_search,
+                                 "what": "unmodified RAGVectorStore.search (ollama_rag_system.py:388-525), 1000 rows (its LIMIT), top-%d" % k},
+                "loop_n10000": {"value": 1.0 / t_loop, "ms_per_query": 1e3 * t_loop, "rows_per_s": len(rows) / t_loop,
+                                "what": "unmodified EmbeddingGenerator.calculate_similarity (:199-222) per row + sorted (:511-515), 10 000 rows x %d" % d},
+                "best_row": int(top[0][0])}
+    except Exception as e:  # the GPU line must not depend on this leg
+        return {"kind": "_ref", "unavailable": f"{type(e).__name__}: {e}"}
+    finally:
+        sys.path.remove(path)
+        sys.modules.pop("ollama_rag_system", None)
+
+
+def cpu_baseline_obj(wl, batch, k, target_s, literal=True):
     qps, t, n_s, cores = cpu_sample(wl["n"], wl["d"], batch, k, target_s)
     lit = literal_rows_per_s(wl["d"], k)
     return {
+        "literal": literal_ref(wl["d"], k) if literal else None,
         "literal_loop": {"rows_per_s": lit, "queries_per_s_extrapolated": lit / wl["n"], "cores": 1,
                          "what": "oracle.search_literal = the reference's per-row Python loop, 3000 rows x 1 query, scaled linearly"},
-        "value": qps, "unit": "queries/s", "cores": cores, "kind": "port",
-        "sample": (f"oracle.search_f64_blocked (numpy float64 GEMM + top-k, all BLAS threads) on {n_s} of "
+        "value": qps, "unit": "queries/s", "cores": cores, "blas_threads": cores, "kind": "port",
+        "sample": (f"oracle.search_f64_blocked (numpy float64 GEMM + top-k, {cores} BLAS threads) on {n_s} of "
                    f"{wl['n']} rows x {wl['d']}, batch {batch}: {t:.2f} s; scaled linearly in rows"),
     }, t
 
@@ -142,7 +223,7 @@ def run_reference(args):
     per = min(args.cpu_seconds, 150.0 / max(1, args.steps + args.warmup))
     vals, secs = [], []
     for i in range(args.warmup + args.steps):
-        obj, t = cpu_baseline_obj(wl, args.batch, args.k, per)
+        obj, t = cpu_baseline_obj(wl, args.batch, args.k, per, literal=(i == args.warmup + args.steps - 1))
         if i >= args.warmup:
             vals.append(obj["value"]); secs.append(t)
     qps = sum(vals) / len(vals)
@@ -325,6 +406,43 @@ def roofline_obj(kind, store, work_per_launch, pk, pk_src, sustained):
             (", sustained" if (kind == "tensor" and sustained) else ", burst" if kind == "tensor" else "")}
 
 
+def per_step(roof, steps, ms_total):
+    """A batch can run as several launches of the dominant kernel (top-100 at batch 4096 is cut into query groups that
+    fill the SM pairs better): `work` is the whole step's, so the rate is per STEP's worth of launches, not per launch."""
+    lps = max(1.0, roof["launches_timed"] / float(steps))
+    roof["achieved"] /= lps
+    roof["frac"] /= lps
+    roof["launches_per_step"] = lps
+    roof["kernel_share_of_step"] = roof["kernel_ms"] * lps / (ms_total / steps)
+
+
+def parity_obj(torch, store, Q, k, dtype, n_sample=32, metric="ip"):
+    """recall_at_k / max_abs_score_err of the device result against the float64 oracle over ALL rows of the store
+    (oracle/parity.py), for a sample of the queries the timed steps used."""
+    import numpy as np
+    from oracle import parity
+    tol = 1e-3 if dtype != "bf16" else 4e-3
+    t0 = time.perf_counter()
+    ids, sc = store.search_dev(Q, k, metric)
+    kk = min(k + 1, len(store))
+    _, sc1 = store.search_dev(Q, kk, metric)
+    torch.cuda.synchronize()
+    ids, sc, sc1 = ids.cpu().numpy(), sc.cpu().numpy(), sc1.cpu().numpy()
+    sample = parity.sample_queries(sc1, k, n_sample) if kk > k else np.arange(min(n_sample, len(ids)))
+    res = parity.check_store(store, Q.cpu().numpy(), ids, sc, k, metric, tol, sample, threads=min(8, host_cores()))
+    res["seconds"] = time.perf_counter() - t0
+    res["oracle"] = "oracle.search_f64_blocked over all %d packed rows pulled back through ragb_store_get_rows" % len(store)
+    res.pop("sampled_queries", None)
+    return res
+
+
+def sustained_obj(torch, dist, step, ms_short, world, local, B, seconds=2.0):
+    n = max(20, int(seconds * 1e3 / max(ms_short, 1e-3)) + 1)
+    with ClockSampler(local) as cs:
+        ms = time_device(torch, dist, step, n, 0, world)
+    return {"steps": n, "ms_per_step": ms / n, "value": B * n / (ms / 1e3), "unit": "queries/s", "clocks": cs.summary()}
+
+
 def bound_of(B, pk):
     """Which roofline bounds a search over 16-bit rows at batch B: every row is read once (2 B per element) and
     costs 2*B flop per element, so the tensor pipe binds above B = peak_flops / peak_bytes (about 250 here)."""
@@ -387,6 +505,7 @@ def run_b200(args):
     tensor_path = bound_of(B, pk) == "tensor"
     work = 2.0 * B * (r1 - r0) * d if tensor_path else float(r1 - r0) * d * 2
     roof = roofline_obj("tensor" if tensor_path else "hbm", store, work, pk, pk_src, sustained=(ms / args.steps > 50.0))
+    per_step(roof, args.steps, ms)
 
     # ---- end-to-end leg (host buffers through the public entry point) ---------------
     if world == 1:
@@ -400,15 +519,26 @@ def run_b200(args):
 
     roof["kernel"] = ("gemm_topk_pair_kernel (tcgen05.mma cta_group::2 + TMA, fused top-k)" if tensor_path
                       else "scan_topk_kernel")
-    attach_traffic(roof, f"{args.workload}_b{B}_n{world}")
-    roof["kernel_share_of_step"] = roof["kernel_ms"] / (ms / args.steps)
+    attach_traffic(roof, f"{args.workload}_b{B}_n{world}" if k == 10 else f"{args.workload}_b{B}_k{k}_n{world}")
+
+    # ---- parity against the float64 oracle on a sample of the timed queries (outside every timed region) -------
+    par = None
+    if rank == 0 and world == 1 and not args.no_parity:
+        par = parity_obj(torch, store, Q, k, wl["dtype"])
+
+    # ---- the same step repeated for >= 2 s: the power-capped steady state the 20-step figure may not reach --------
+    sustained = None
+    if not args.no_sustained:
+        sustained = sustained_obj(torch, dist, step, ms / args.steps, world, local, B)
 
     extras = []
-    if rank == 0 and world == 1 and not args.no_extras:
+    if world == 1 and not args.no_extras:
         extras = run_extras(args, pkg, torch, store, wl, pk, pk_src)
+    elif not args.no_extras:
+        extras = run_extras_sharded(args, pkg, torch, dist, searcher, store, wl, pk, pk_src, world, rank, local)
 
     cpu = None
-    if rank == 0 and world == 1 and not args.no_cpu:
+    if rank == 0 and not args.no_cpu:   # rank 0 alone; BLAS threads pinned explicitly (torchrun exports OMP_NUM_THREADS=1)
         cpu, _ = cpu_baseline_obj(wl, B, k, args.cpu_seconds)
 
     if world > 1:
@@ -431,6 +561,8 @@ def run_b200(args):
                        "l2": f"corpus shard {(r1 - r0) * d * 2 / 1e6:.0f} MB per GPU vs 126 MB L2: no flush needed"
                              if (r1 - r0) * d * 2 > 4 * 126e6 else "corpus shard comparable to L2; not flushed"},
             "e2e": e2e, "roofline": roof, "cpu_baseline": cpu, "gpu_launches": launches, "clocks": clocks,
+            "recall_at_k": par and par["recall_at_k"], "max_abs_score_err": par and par["max_abs_score_err"],
+            "parity_queries": par and par["parity_queries"], "parity": par, "sustained": sustained,
             "extras": extras,
         }
         print(json.dumps(line), flush=True)

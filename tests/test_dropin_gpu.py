@@ -175,7 +175,10 @@ def test_add_document_worker_thread_and_add_documents(ref_modules, tmp_path):
             r = rs.query(texts[i], max_results=1)
             assert r.documents[0].metadata["i"] == i and abs(r.similarities[0] - 1.0) < 1e-3
         many = rs.query_many([texts[i] for i in range(60)], max_results=1)
-        assert [r.documents[0].metadata["i"] for r in many] == list(range(60))
+        # document 11 is the zero vector (cosine 0.0 everywhere: nothing reaches 0.7, :214-215); 23, 30 and 57 are
+        # identical vectors: the newest wins the tie (:474, :512)
+        want = [None if i == 11 else 57 if i in (23, 30) else i for i in range(60)]
+        assert [r.documents[0].metadata["i"] if r.documents else None for r in many] == want
         rs.shutdown()
         st = rs.get_system_stats()
     assert st['vector_store']['total_documents'] == 60 and st['vector_store']['backend'] == 'b200+sqlite'
@@ -268,7 +271,9 @@ def test_enhanced_rag_system_paths(ref_modules, tmp_path):
         plain.embedding_generator.embedding_cache["what do my notes say?"] = pickle.loads(blob)
         want = plain.search(ref.RAGQuery(query_text="what do my notes say?", context={}, max_results=5,
                                          similarity_threshold=0.7))
-    assert len(fast.documents) >= 1 and fast.documents[0].content == content
+    # (the five notes differ in one digit: their FallbackEmbedder vectors tie within the fp16 rounding)
+    hit = [s for d, s in zip(fast.documents, fast.similarities) if d.content == content]
+    assert len(hit) == 1 and abs(hit[0] - 1.0) < 1e-3
     _same_result(want, fast, ref, k=5, what="enhanced_query")
     assert out['query'] == "what do my notes say?" and 'enhancement_insights' in out
     store.close(save=False)
