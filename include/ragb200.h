@@ -19,6 +19,15 @@
  *     ollama_rag_system.py:474,512).
  *   - there is no CPU fallback: without a CUDA device every compute entry point
  *     fails with RAGB_ECUDA.
+ *   - threads: every entry point may be called from any thread.  Searches of different threads run side by side
+ *     (each leases its own stream + workspace from the store; the reference's GUI spawns a thread per query,
+ *     rag_query_interface.py:740-744, against one ingest thread, ollama_rag_system.py:652); appends are serialised
+ *     among themselves and run beside searches; calls that rewrite what a search reads (set, set_meta,
+ *     set_timestamps, build_filter, reserve, clear) wait for the searches in flight.
+ *   - streams: work launched on a caller's stream by a "_dev" entry point is ordered for the caller: rows appended
+ *     with ragb_store_add*_dev are searchable by every later call on any stream or thread (the store records an
+ *     event behind the ingest kernel and later searches wait for it), and a later search that reuses the
+ *     workspace of an earlier caller-stream search waits for that search first.
  */
 #ifndef RAGB200_H
 #define RAGB200_H
@@ -29,7 +38,7 @@
 extern "C" {
 #endif
 
-#define RAGB_ABI_VERSION 1
+#define RAGB_ABI_VERSION 2
 
 /* element types */
 #define RAGB_F16 0
@@ -145,6 +154,14 @@ int ragb_store_set_meta(ragb_store* s, int64_t row0, int64_t n, const uint8_t* f
                         const uint16_t* src); /* host arrays; NULL = leave unchanged */
 int ragb_store_build_filter(ragb_store* s, const uint8_t* src_allowed, int n_codes, int64_t window,
                             int64_t* out_total);
+/* Per-row timestamps (fp64, the reference's RAGDocument.timestamp, ollama_rag_system.py:53) for "ORDER BY timestamp DESC"
+ * (:474) and for the order among equal scores (:512: the stable sort keeps the SQL order, newer first).  While
+ * timestamps do not decrease in row order nothing changes (newer == larger row).  When they do, the store sorts
+ * (timestamp, row) on the device (csrc/rank.cuh) and from then on every candidate key carries the row's recency rank
+ * instead of its row number: the window of build_filter is the newest rows BY TIMESTAMP and equal scores come back
+ * newest timestamp first, later row first among equal timestamps — no host mask, no host re-sort.  Rows that were
+ * never described count as the newest so far, in row order. */
+int ragb_store_set_timestamps(ragb_store* s, int64_t row0, int64_t n, const double* ts);
 
 /* ---- measurement ------------------------------------------------------------
  * While enabled, every search call brackets its dominant kernel (the scan for the
@@ -191,6 +208,56 @@ int ragb_search_scatter_dev(ragb_store* s, const float* q, int64_t nq, int k, in
                             void* stream);
 int ragb_gather_merge_dev(int device, const ragb_exchange* x, int64_t nq, int k, float* out_scores,
                           int64_t* out_ids, int* out_status, void* stream);
+
+/* ---- row-sharded store: ONE process, the rows dealt over several GPUs of one NVSwitch box ------------------------
+ * north_star: "the embedding store ... row-sharded across GPUs", behind the same entry points as the one-device store
+ * (RAGVectorStore.add_document / search, ollama_rag_system.py:372-386 / :388-403).
+ *   layout  rows are dealt to the devices in blocks of block_rows (a power of two >= 2048; 0 = 16384), round-robin:
+ *           global row g lives on device (g / block_rows) % n_dev at local row (g / block_rows / n_dev) * block_rows
+ *           + g % block_rows, so shards stay within one block of balanced while the store grows, and global <-> local
+ *           is arithmetic (no table).
+ *   search  the queries go to every device, each runs its local scan / tcgen05 kernel, and the LAST kernel of every
+ *           device stores its k candidates per query — keys whose low word is the GLOBAL row — straight into the gather
+ *           buffer on the first device through peer-mapped memory (NVLink P2P stores, no collective, no staging
+ *           copy); one merge kernel on the first device finishes.  Results equal the one-device store's, ties included.
+ *   policy  set_meta / build_filter as for ragb_store (the newest-`window` cut is taken over the GLOBAL row order);
+ *           timestamps must not decrease in row order (out-of-order timestamps need the recency ranks of a
+ *           one-device store: RAGB_EUNSUPPORTED).
+ * `valid` for the search entry points: NULL, RAGB_STORE_FILTER, or (host entry only) a mask over global rows.
+ * A device may be listed more than once (several shards on one GPU; the tests cover the layout that way on one GPU). */
+typedef struct ragb_mstore ragb_mstore;
+int ragb_mstore_create(int dim, int dtype, int64_t capacity, const int* device_ids, int n_dev, int64_t block_rows,
+                       ragb_mstore** out);
+int ragb_mstore_destroy(ragb_mstore* m);
+int ragb_mstore_reserve(ragb_mstore* m, int64_t capacity);
+int ragb_mstore_clear(ragb_mstore* m);
+int64_t ragb_mstore_size(const ragb_mstore* m);
+int64_t ragb_mstore_capacity(const ragb_mstore* m);
+int64_t ragb_mstore_block_rows(const ragb_mstore* m);
+int ragb_mstore_n_devices(const ragb_mstore* m);
+int ragb_mstore_device(const ragb_mstore* m, int i);          /* CUDA ordinal of shard i */
+int64_t ragb_mstore_device_rows(const ragb_mstore* m, int i); /* rows held by shard i */
+int ragb_mstore_add(ragb_mstore* m, const float* rows, int64_t n, int64_t* out_first_row);
+/* rows on ANY device of the box (peer access): each shard's ingest kernel reads its blocks over NVLink; `stream` (on
+ * the rows' device; NULL = none) is synchronised first */
+int ragb_mstore_add_dev(ragb_mstore* m, const void* rows, int in_dtype, int64_t n, int64_t ld_in,
+                        int64_t* out_first_row, void* stream);
+int ragb_mstore_set(ragb_mstore* m, int64_t row, const float* vec);
+int ragb_mstore_get_rows(ragb_mstore* m, int64_t row0, int64_t n, void* out_rows, float* out_norms);
+int ragb_mstore_put_rows(ragb_mstore* m, const void* packed_rows, const float* norms, int64_t n,
+                         int64_t* out_first_row);
+int ragb_mstore_set_meta(ragb_mstore* m, int64_t row0, int64_t n, const uint8_t* flags, const uint16_t* src);
+int ragb_mstore_set_timestamps(ragb_mstore* m, int64_t row0, int64_t n, const double* ts);
+int ragb_mstore_build_filter(ragb_mstore* m, const uint8_t* src_allowed, int n_codes, int64_t window,
+                             int64_t* out_total);
+int ragb_mstore_search(ragb_mstore* m, const float* q, int64_t nq, int k, int metric, float threshold, int flags,
+                       const uint8_t* valid, float* out_scores, int64_t* out_ids);
+/* q, out_scores, out_ids on the FIRST device of the store; stream on that device (NULL = synchronous) */
+int ragb_mstore_search_dev(ragb_mstore* m, const float* q, int64_t nq, int k, int metric, float threshold,
+                           int flags, const uint8_t* valid, float* out_scores, int64_t* out_ids, void* stream);
+int ragb_mstore_profile(ragb_mstore* m, int enable);
+/* total_ms: the slowest shard's summed dominant-kernel time; n_launches: bracketed launches of the first shard */
+int ragb_mstore_profile_read(ragb_mstore* m, double* total_ms, int64_t* n_launches);
 
 #ifdef __cplusplus
 }

@@ -13,6 +13,7 @@ from pathlib import Path
 CSRC = Path(__file__).resolve().parent / "csrc"
 LIB_PATH = Path(os.environ["RAGB200_LIB"]) if os.environ.get("RAGB200_LIB") else CSRC / "libragb200.so"  # override: A/B runs of build variants
 
+ABI_VERSION = 2
 F16, BF16, F32 = 0, 1, 2
 MASK_U8, MASK_I32, MASK_I64, MASK_F32 = 0, 1, 2, 3
 IP, COSINE = 0, 1
@@ -63,6 +64,7 @@ SIGNATURES = {
     "ragb_search_dev": (_i, [_vp, _vp, _i64, _i, _i, _f, _i, _i64, _i64, _vp, _vp, _vp, _vp]),
     "ragb_store_set_meta": (_i, [_vp, _i64, _i64, _vp, _vp]),
     "ragb_store_build_filter": (_i, [_vp, _vp, _i, _i64, _pi64]),
+    "ragb_store_set_timestamps": (_i, [_vp, _i64, _i64, _vp]),
     "ragb_store_profile": (_i, [_vp, _i]),
     "ragb_store_profile_read": (_i, [_vp, C.POINTER(C.c_double), _pi64]),
     "ragb_kpad": (_i, [_i]),
@@ -70,6 +72,29 @@ SIGNATURES = {
     "ragb_merge_keys_dev": (_i, [_i, _vp, _i64, _i, _i, _i64, _i64, _i, _vp, _vp, _vp]),
     "ragb_search_scatter_dev": (_i, [_vp, _vp, _i64, _i, _i, _f, _i, _i64, _i64, _vp, C.c_uint32, C.POINTER(Exchange), _vp]),
     "ragb_gather_merge_dev": (_i, [_i, C.POINTER(Exchange), _i64, _i, _vp, _vp, _vp, _vp]),
+    # row-sharded store (one process, several GPUs)
+    "ragb_mstore_create": (_i, [_i, _i, _i64, C.POINTER(_i), _i, _i64, C.POINTER(_vp)]),
+    "ragb_mstore_destroy": (_i, [_vp]),
+    "ragb_mstore_reserve": (_i, [_vp, _i64]),
+    "ragb_mstore_clear": (_i, [_vp]),
+    "ragb_mstore_size": (_i64, [_vp]),
+    "ragb_mstore_capacity": (_i64, [_vp]),
+    "ragb_mstore_block_rows": (_i64, [_vp]),
+    "ragb_mstore_n_devices": (_i, [_vp]),
+    "ragb_mstore_device": (_i, [_vp, _i]),
+    "ragb_mstore_device_rows": (_i64, [_vp, _i]),
+    "ragb_mstore_add": (_i, [_vp, _vp, _i64, _pi64]),
+    "ragb_mstore_add_dev": (_i, [_vp, _vp, _i, _i64, _i64, _pi64, _vp]),
+    "ragb_mstore_set": (_i, [_vp, _i64, _vp]),
+    "ragb_mstore_get_rows": (_i, [_vp, _i64, _i64, _vp, _vp]),
+    "ragb_mstore_put_rows": (_i, [_vp, _vp, _vp, _i64, _pi64]),
+    "ragb_mstore_set_meta": (_i, [_vp, _i64, _i64, _vp, _vp]),
+    "ragb_mstore_set_timestamps": (_i, [_vp, _i64, _i64, _vp]),
+    "ragb_mstore_build_filter": (_i, [_vp, _vp, _i, _i64, _pi64]),
+    "ragb_mstore_search": (_i, [_vp, _vp, _i64, _i, _i, _f, _i, _vp, _vp, _vp]),
+    "ragb_mstore_search_dev": (_i, [_vp, _vp, _i64, _i, _i, _f, _i, _vp, _vp, _vp, _vp]),
+    "ragb_mstore_profile": (_i, [_vp, _i]),
+    "ragb_mstore_profile_read": (_i, [_vp, C.POINTER(C.c_double), _pi64]),
 }
 
 
@@ -80,8 +105,10 @@ class RagbError(RuntimeError):
 
 
 def build(force: bool = False) -> Path:
-    """Compile csrc/ragb200.cu -> csrc/libragb200.so for sm_100a (nvcc cross-compiles without a GPU)."""
-    srcs = list(CSRC.glob("*.cu")) + list(CSRC.glob("*.cuh")) + [CSRC.parent.parent / "include" / "ragb200.h"]
+    """Compile csrc/*.cu -> csrc/libragb200.so for sm_100a (make -j: one translation unit per kernel family; nvcc
+    cross-compiles without a GPU)."""
+    srcs = (list(CSRC.glob("*.cu")) + list(CSRC.glob("*.cuh")) + list(CSRC.glob("*.h")) + [CSRC / "Makefile"] +
+            [CSRC.parent.parent / "include" / "ragb200.h"])
     if not force and LIB_PATH.exists() and all(LIB_PATH.stat().st_mtime >= s.stat().st_mtime for s in srcs):
         return LIB_PATH
     subprocess.run(["bash", str(CSRC / "build.sh")], check=True)
@@ -103,7 +130,7 @@ def lib() -> C.CDLL:
         for name, (res, args) in SIGNATURES.items():
             fn = getattr(l, name)
             fn.restype, fn.argtypes = res, args
-        if l.ragb_abi_version() != 1:
+        if l.ragb_abi_version() != ABI_VERSION:
             raise ImportError("libragb200.so ABI version mismatch; rebuild")
         _lib = l
     return _lib

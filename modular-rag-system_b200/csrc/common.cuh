@@ -39,6 +39,32 @@ __device__ __forceinline__ float key_score(uint64_t k) { return unorder_bits((ui
 __device__ __forceinline__ uint32_t key_id(uint64_t k) { return (uint32_t)k; }
 
 // ---------------------------------------------------------------------------
+// The id carried in the low word of a key.  One device, timestamps in row order: the row itself (+ base).
+// Row-sharded store (mstore.cu): rows are dealt to the devices in blocks of 2^shift rows, round-robin, so the GLOBAL row
+// of a local row is arithmetic.  Non-monotone timestamps: a per-row recency RANK (position of the row in
+// (timestamp, row) order — what "ORDER BY timestamp DESC" + the stable sort of ollama_rag_system.py:474,512 rank equal
+// scores by), decoded back to the row through the inverse permutation when the winners are written out.
+// ---------------------------------------------------------------------------
+struct IdMap {
+  const uint32_t* rank;  // [rows] id of every local row, or null
+  uint32_t base;         // rank == null: id = global_row(row) + base
+  int shift;             // >= 0: block-cyclic shard, block = 2^shift rows; < 0: global_row = row
+  int n_dev, dev;
+};
+__host__ __device__ __forceinline__ uint32_t global_row(const IdMap& m, uint32_t r) {
+  if (m.shift < 0) return r;
+  return ((((r >> m.shift) * (uint32_t)m.n_dev + (uint32_t)m.dev) << m.shift) | (r & ((1u << m.shift) - 1u)));
+}
+__device__ __forceinline__ uint32_t map_id(const IdMap& m, int64_t row) {
+  if (m.rank) return m.rank[row];
+  return global_row(m, (uint32_t)row) + m.base;
+}
+// id -> what the caller sees (row_of_id = inverse of the rank permutation, or null)
+__device__ __forceinline__ int64_t decode_id(const uint32_t* row_of_id, uint32_t id) {
+  return row_of_id ? (int64_t)row_of_id[id] : (int64_t)id;
+}
+
+// ---------------------------------------------------------------------------
 // Candidate exchange over peer memory (row-sharded corpus, one process per GPU).
 // The kernel that produces a rank's final keys stores them straight into EVERY rank's gather buffer
 // (its own included) through peer-mapped pointers — NVLink P2P stores, no collective launch — and the

@@ -7,28 +7,17 @@
 // embedding) and a 16-bit source code — and these kernels turn (allowed sources, window) into the
 // per-row `valid` bytes the search kernels read, without a per-query host pass over all rows and
 // without shipping a mask over PCIe.  The window is "the newest W matching rows" = the LAST W matches
-// in row order; that is exact when timestamps are non-decreasing in row order (the host shim checks
-// this and falls back to a host-built mask otherwise).
+// in RECENCY order: position p of that order holds row perm[p] (rank.cuh: rows sorted by (timestamp,
+// row)); while timestamps do not decrease in row order perm is null and position == row.
 #pragma once
 #include "common.cuh"
+#include "params.h"
 
 namespace ragb {
 
-constexpr int kFilterThreads = 256;
-constexpr int kFilterRowsPerCta = 2048;  // 8 rows per thread
 
-struct FilterParams {
-  const uint8_t* flags;        // [n] bit0 live, bit1 has embedding
-  const uint16_t* src;         // [n] source code
-  const uint8_t* src_allowed;  // [n_codes] or null = every source
-  int n_codes;
-  int64_t n;
-  int64_t window;              // < 0: no window
-  uint8_t* valid;              // [n] out
-  unsigned* counts;            // [ceil(n / kFilterRowsPerCta)] matches per CTA
-  int64_t* result;             // [0] total rows the SQL would return, [1] cut CTA, [2] matches to keep in the cut CTA
-};
 
+__device__ __forceinline__ int64_t filter_row(const FilterParams& p, int64_t pos) { return p.perm ? (int64_t)p.perm[pos] : pos; }
 __device__ __forceinline__ bool filter_match(const FilterParams& p, int64_t r) {
   if (!(p.flags[r] & 1)) return false;
   if (!p.src_allowed) return true;
@@ -42,8 +31,8 @@ __global__ void __launch_bounds__(kFilterThreads) filter_mark_kernel(const Filte
   const int64_t base = (int64_t)blockIdx.x * kFilterRowsPerCta;
   unsigned cnt = 0;
   for (int i = threadIdx.x; i < kFilterRowsPerCta; i += kFilterThreads) {
-    const int64_t r = base + i;
-    if (r < p.n) {
+    if (base + i < p.n) {
+      const int64_t r = filter_row(p, base + i);
       const bool m = filter_match(p, r);
       cnt += m ? 1u : 0u;
       p.valid[r] = (m && (p.flags[r] & 2)) ? 1 : 0;
@@ -95,13 +84,15 @@ __global__ void __launch_bounds__(1024) filter_cut_kernel(const FilterParams p, 
 }
 
 // pass 3: rows older than the window are cleared; inside the cut CTA only its last result[2] matches stay
+// (result[1], result[2] come from pass 2 — or from the host, which merges the per-CTA counts of several devices when
+// the rows are sharded, mstore.cu)
 __global__ void __launch_bounds__(kFilterThreads) filter_window_kernel(const FilterParams p) {
   const int64_t cut = p.result[1];
   if (cut < 0 || (int64_t)blockIdx.x > cut) return;
   const int64_t base = (int64_t)blockIdx.x * kFilterRowsPerCta;
   if ((int64_t)blockIdx.x < cut) {
     for (int i = threadIdx.x; i < kFilterRowsPerCta; i += kFilterThreads)
-      if (base + i < p.n) p.valid[base + i] = 0;
+      if (base + i < p.n) p.valid[filter_row(p, base + i)] = 0;
     return;
   }
   // the cut CTA: thread t owns rows [t*8, t*8+8); suffix counts of matches decide who stays
@@ -111,23 +102,23 @@ __global__ void __launch_bounds__(kFilterThreads) filter_window_kernel(const Fil
   unsigned c = 0;
 #pragma unroll
   for (int j = 0; j < kPer; ++j) {
-    const int64_t r = base + threadIdx.x * kPer + j;
-    m[j] = r < p.n && filter_match(p, r);
+    const int64_t pos = base + threadIdx.x * kPer + j;
+    m[j] = pos < p.n && filter_match(p, filter_row(p, pos));
     c += m[j] ? 1u : 0u;
   }
   tcnt[threadIdx.x] = c;
   __syncthreads();
   unsigned after = 0;  // matches in rows owned by later threads
   for (int t = threadIdx.x + 1; t < kFilterThreads; ++t) after += tcnt[t];
-  const unsigned keep = (unsigned)p.result[2];
+  const unsigned keep = (unsigned)min(p.result[2], (int64_t)kFilterRowsPerCta);
 #pragma unroll
   for (int j = kPer - 1; j >= 0; --j) {
-    const int64_t r = base + threadIdx.x * kPer + j;
+    const int64_t pos = base + threadIdx.x * kPer + j;
     if (m[j]) {
       ++after;                        // this row is the `after`-th match from the end of the CTA
-      if (after > keep) p.valid[r] = 0;
-    } else if (r < p.n) {
-      p.valid[r] = 0;
+      if (after > keep) p.valid[filter_row(p, pos)] = 0;
+    } else if (pos < p.n) {
+      p.valid[filter_row(p, pos)] = 0;
     }
   }
 }

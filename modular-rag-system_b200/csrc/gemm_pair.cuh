@@ -23,11 +23,6 @@
 
 namespace ragb {
 
-constexpr int kPairStagesSmall = 5;              // ring depth next to the shared-memory candidate buffers (kpad <= 32)
-constexpr int kPairStagesLarge = 6;              // kpad 64 / 128: candidates live in global memory
-constexpr int kPairN = 256;                       // corpus rows per accumulator tile (both halves)
-constexpr int kPairStageBytes = 2 * kStageBytesA; // 16 KB queries + 16 KB half corpus tile
-constexpr int kPairSyncTiles = 8;                 // default tiles between two meetings of the pairs that share a row split
 constexpr uint32_t kPeerBitMask = 0xFEFFFFFFu;    // shared::cluster address of the even (leader) CTA of a pair
 
 __device__ __forceinline__ void tma_load_2d_pair(void* dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1) {
@@ -79,8 +74,6 @@ __device__ __forceinline__ void mbar_wait_cluster(uint64_t* bar, uint32_t parity
 //   E == 2 : kpad <= 32, 48 slots in shared memory, pruned by warp_top32_of_64
 //   E == 4 : kpad == 64, E == 8 : kpad == 128 — 32*E slots in GLOBAL memory (L2 resident; an insert is a rare
 //            event, about k*ln(rows/k) per query over a CTA's lifetime), pruned by a register bitonic sort
-constexpr int kPairCapSmall = 64;
-constexpr int kPairCapSmallQ = 48;  // next to a resident query tile: k <= 32 survivors + the 16 chunks one tile can add
 template <int E, bool Q = false> struct CandCfg {
   static constexpr int cap = E == 2 ? (Q ? kPairCapSmallQ : kPairCapSmall) : 32 * E;
   static constexpr int stride = E == 2 ? cap + 1 : 32 * E;  // +1: conflict-free for both access patterns
@@ -90,17 +83,10 @@ template <int E, bool Q = false> struct CandCfg {
 // query k-block with every corpus k-block doubles the L2 -> SM bytes (measured at 12.5M x 384, B=4096, top-100:
 // 154 GB per launch over the crossbar = 15.6 TB/s at full tensor rate, more than L2 delivers; the MMA warp waited
 // for TMA 22 % of the time, tensor pipe 60 % active).  With the tile resident the ring moves 16 KB per k-block.
-constexpr int kPairQResMaxKB = 6;
-constexpr int kPairStagesSmallQ = 5;   // x 16 KB, next to 96 KB of queries and the 49 KB of candidate buffers
-constexpr int kPairStagesLargeQ = 8;   // x 16 KB, next to 96 KB of queries
 // rows behind one candidate key: 16 — half of one tcgen05.ld of 32 columns; the finish kernel then re-reads half as
 // many rows (1M x 384, B=1024, top-10: 133 -> 96 us).  For k > 32 this used to lose (twice the inserts into the
 // global-memory buffers, +8 % at 1M x 384 top-100 with the full-sort prune); with the sorted-prefix prune it wins or
 // ties: 1M x 384 top-100 B=1024 1.96 -> 1.77 ms, 10M x 768 13.7 -> 13.4 ms, 12.5M x 384 B=4096 33.4 -> 33.6 ms.
-#ifndef RAGB_CHUNK_ROWS_LARGE
-#define RAGB_CHUNK_ROWS_LARGE 16  // build-time A/B: -DRAGB_CHUNK_ROWS_LARGE=32
-#endif
-template <int E> struct ChunkCfg { static constexpr int rows = E == 2 ? 16 : RAGB_CHUNK_ROWS_LARGE; };
 
 __device__ __forceinline__ float fmax3(float a, float b, float c) {
   float r;

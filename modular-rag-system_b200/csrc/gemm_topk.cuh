@@ -19,17 +19,10 @@
 #include <cuda.h>
 
 #include "common.cuh"
+#include "params.h"
 
 namespace ragb {
 
-constexpr int kGemmM = 128;       // queries per CTA
-constexpr int kGemmN = 256;       // rows per MMA tile
-constexpr int kGemmKB = 64;       // elements per k-block (128 bytes = one swizzle row)
-constexpr int kGemmThreads = 192;
-constexpr int kStageBytesA = kGemmM * kGemmKB * 2;
-constexpr int kStageBytesB = kGemmN * kGemmKB * 2;
-constexpr int kStageBytes = kStageBytesA + kStageBytesB;
-constexpr int kGemmMaxKpad = 32;  // per-thread lists live in shared memory
 
 // ---- PTX wrappers ---------------------------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -101,16 +94,6 @@ __device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t smem_addr) {
   d |= (uint64_t)2 << 61;                       // SWIZZLE_128B
   return d;
 }
-// kind::f16 instruction descriptor: fp32 accumulate, A and B K-major, dense
-__host__ __device__ inline uint32_t umma_idesc(bool bf16, int M, int N) {
-  uint32_t d = 0;
-  d |= 1u << 4;                     // D format: F32
-  d |= (bf16 ? 1u : 0u) << 7;       // A format
-  d |= (bf16 ? 1u : 0u) << 10;      // B format
-  d |= (uint32_t)(N >> 3) << 17;
-  d |= (uint32_t)(M >> 4) << 24;
-  return d;
-}
 
 // ---- query conversion: fp32 -> fp16/bf16, pre-scaled by 1/|q| for the cosine metric --------
 template <typename T>
@@ -134,19 +117,6 @@ __global__ void __launch_bounds__(128) convert_queries_kernel(const float* __res
   for (int i = lane; i < ld_out; i += 32) dst[i] = Elem<T>::from_float(i < dim ? src[i] * scale : 0.f);
 }
 
-struct GemmParams {
-  int dim;
-  int64_t row_begin, row_end;  // absolute rows
-  const uint8_t* valid;
-  int64_t nq;
-  int n_qt, n_splits;          // grid = n_qt * n_splits, block b: qt = b % n_qt, split = b / n_qt
-  int64_t n_tiles;             // row tiles of kGemmN over [row_begin,row_end)
-  int flags;
-  float threshold;
-  int k, kpad, stages;
-  uint32_t id_base, idesc;
-  uint64_t* out;               // [n_qt*128][n_splits][kpad] sorted keys
-};
 
 // ---- per-thread (per-query) candidate list in shared memory: list[j*128 + tid] ---------------
 struct EpiList {
@@ -154,7 +124,7 @@ struct EpiList {
   int k, cnt, thr_pos;
   uint64_t thr_key;   // smallest held key once k are held, else 0
 };
-__device__ __noinline__ void epi_insert(EpiList& L, uint64_t key) {
+static __device__ __noinline__ void epi_insert(EpiList& L, uint64_t key) {
   if (L.cnt < L.k) {
     L.slot[L.cnt * kGemmM] = key;
     if (++L.cnt < L.k) return;
@@ -173,6 +143,8 @@ __device__ __noinline__ void epi_insert(EpiList& L, uint64_t key) {
 // raw score a candidate must reach before the exact (slow) test is worth running
 __device__ __forceinline__ float fast_bound(float t, int flags) { return ((flags & 1) && t <= 0.f) ? -INFINITY : t; }
 
+// (a template only so that the kernel is instantiated in ONE translation unit, k_gemm.cu, although several include this header)
+template <int kUnused>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_topk_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_x, const GemmParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -319,8 +291,8 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constan
 template <typename T>
 __global__ void __launch_bounds__(256) rescore_kernel(const T* __restrict__ X, int64_t ld, int dim,
                                                       const float* __restrict__ q, int64_t nq, int metric, int flags,
-                                                      float threshold, uint32_t id_base, int kpad,
-                                                      uint64_t* __restrict__ keys /* [nq][kpad] in/out */) {
+                                                      float threshold, IdMap ids, int kpad,
+                                                      uint64_t* __restrict__ keys /* [nq][kpad]: LOCAL rows in, ids out */) {
   const int64_t w = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
   const int lane = threadIdx.x & 31;
   if (w >= nq * kpad) return;
@@ -329,7 +301,7 @@ __global__ void __launch_bounds__(256) rescore_kernel(const T* __restrict__ X, i
   const int64_t qi = w / kpad;
   const float* qv = q + qi * dim;
   const uint32_t id = key_id(key);
-  const T* row = X + (size_t)(id - id_base) * ld;
+  const T* row = X + (size_t)id * ld;
   float dot = 0.f, qq = 0.f;
   for (int i = lane; i < dim; i += 32) {
     const float a = qv[i];
@@ -341,38 +313,7 @@ __global__ void __launch_bounds__(256) rescore_kernel(const T* __restrict__ X, i
   const float scale = metric == 1 ? (qq > 0.f ? rsqrtf(qq) : 0.f) : 1.f;
   const float sc = finish_score(dot, scale, flags);
   // a winner whose exact score falls just below the threshold is dropped, as the scan would
-  if (lane == 0) keys[w] = sc >= threshold ? make_key(sc, id) : 0;
-}
-
-struct GemmState {
-  CUtensorMap map_x;
-  const void* map_rows = nullptr;  // allocation the map was built for
-  int64_t map_capacity = -1;
-  void* qh = nullptr;              // converted queries
-  size_t qh_bytes = 0;
-  void* encode_fn = nullptr;       // cuTensorMapEncodeTiled
-  // query-stationary kernel (gemm_ts.cuh)
-  CUtensorMap map_x_ts;
-  const void* ts_rows = nullptr;
-  int64_t ts_capacity = -1;
-  int ts_nt = 0;
-  // SM-pair kernel (gemm_pair.cuh)
-  CUtensorMap map_x_pair;
-  const void* pair_rows = nullptr;
-  int64_t pair_capacity = -1;
-  void* sync_ctr = nullptr;        // per-split meeting counters of the pair kernel
-  size_t sync_ctr_bytes = 0;
-  int pair_clusters[6] = {0, 0, 0, 0, 0, 0};  // co-resident SM pairs per kernel variant (kpad <= 32, 64, 128)
-  int occ_c = 0, occ_clusters = 0;
-  size_t occ_smem = 0;
-};
-inline void gemm_state_free(GemmState* g) {
-  if (g->qh) cudaFree(g->qh);
-  if (g->sync_ctr) cudaFree(g->sync_ctr);
-  g->sync_ctr = nullptr; g->sync_ctr_bytes = 0;
-  g->qh = nullptr; g->qh_bytes = 0; g->map_rows = nullptr; g->map_capacity = -1;
-  g->ts_rows = nullptr; g->ts_capacity = -1; g->ts_nt = 0;
-  g->pair_rows = nullptr; g->pair_capacity = -1;
+  if (lane == 0) keys[w] = sc >= threshold ? make_key(sc, map_id(ids, id)) : 0;
 }
 
 }  // namespace ragb

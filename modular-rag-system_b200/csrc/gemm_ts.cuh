@@ -29,36 +29,7 @@
 
 namespace ragb {
 
-constexpr int kTsCap = 64;               // candidate slots per query
-constexpr int kTsCandStride = kTsCap + 1;  // +1: conflict-free for both access patterns
-constexpr int kTsMaxStages = 8;
 
-struct TsParams {
-  const void* qh;       // converted queries [n_qt*128][ld_q], 16-bit elements, zero padded
-  int64_t ld_q;
-  int n_kb;             // 64-element k-blocks (ceil(dim/64))
-  int nt;               // corpus rows per accumulator tile: 32 / 64 / 128
-  int kbs;              // k-blocks per stage
-  int stages;
-  int cluster;          // CTAs per cluster: 1, 2, 4, 8
-  int64_t row_begin, row_end;
-  const uint8_t* valid;
-  int64_t nq;
-  int n_qt, n_splits;
-  int64_t n_tiles;      // tiles of nt rows over [row_begin,row_end)
-  int flags;
-  float threshold;
-  int k, kpad;
-  uint32_t id_base, idesc;
-  uint64_t* out;        // [n_qt*128][n_splits][kpad] sorted keys
-  uint64_t* cand_ws;    // pair kernel, kpad > 32: [grid][128][2*kpad] candidate buffers in global memory
-  float sel_slack;      // pair kernel: slack under the user threshold for the 16-bit-query selection pass
-  int sync_tiles;       // pair kernel: tiles between two meetings
-  int full_sort;        // pair kernel, k > 32: 1 = every prune sorts the whole buffer (A/B switch RAGB_PAIR_FULLSORT)
-  unsigned* gthr;       // pair kernel: [n_qt*128] zeroed per launch, or null — running threshold shared by the row splits
-  unsigned* sync_ctr;   // pair kernel: [n_splits] zeroed per launch, or null — the SM pairs that stream the same row
-                        // split meet every kPairSyncTiles tiles so that they keep hitting each other's rows in L2
-};
 
 __device__ __forceinline__ void tma_load_2d_mc(void* dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1,
                                                uint16_t mask) {

@@ -1,0 +1,8 @@
+// k_pair_e2.cu — instantiations of gemm_topk_pair_kernel<2, ...> (gemm_pair.cuh)
+#include "gemm_pair.cuh"
+#include "kernels.h"
+namespace ragb {
+const void* k_pair_e2(bool qres) {
+  return qres ? (const void*)gemm_topk_pair_kernel<2, kPairStagesSmallQ, true> : (const void*)gemm_topk_pair_kernel<2, kPairStagesSmall, false>;
+}
+}  // namespace ragb

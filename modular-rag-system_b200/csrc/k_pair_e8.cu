@@ -1,0 +1,8 @@
+// k_pair_e8.cu — instantiations of gemm_topk_pair_kernel<8, ...> (gemm_pair.cuh)
+#include "gemm_pair.cuh"
+#include "kernels.h"
+namespace ragb {
+const void* k_pair_e8(bool qres) {
+  return qres ? (const void*)gemm_topk_pair_kernel<8, kPairStagesLargeQ, true> : (const void*)gemm_topk_pair_kernel<8, kPairStagesLarge, false>;
+}
+}  // namespace ragb

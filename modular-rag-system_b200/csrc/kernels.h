@@ -1,0 +1,40 @@
+// kernels.h — the kernels of this library as plain function pointers.
+//
+// Every kernel template is instantiated in exactly one translation unit (k_*.cu), which are compiled in parallel
+// (Makefile) and cost minutes of ptxas time between them; the host side (ragb200.cu, mstore.cu) only sees
+// `const void*` entry points and launches them with cudaLaunchKernel / cudaLaunchKernelExC, so editing host logic
+// never recompiles a kernel.  The argument lists are the kernels' own (see the .cuh each getter names).
+#pragma once
+
+namespace ragb {
+
+// gemm_pair.cuh: gemm_topk_pair_kernel<E, stages, qres>(CUtensorMap map_q, CUtensorMap map_x, TsParams)
+const void* k_pair_e2(bool qres);
+const void* k_pair_e4(bool qres);
+const void* k_pair_e8(bool qres);
+inline const void* k_pair(int E, bool qres) { return E == 2 ? k_pair_e2(qres) : E == 4 ? k_pair_e4(qres) : k_pair_e8(qres); }
+// gemm_ts.cuh / gemm_topk.cuh (single-CTA fallbacks), query conversion, fp32 re-score
+const void* k_ts(bool ts);                  // gemm_topk_ts_kernel<ts>(map_q, map_x, TsParams)
+const void* k_gemm_topk();                  // gemm_topk_kernel(map_q, map_x, GemmParams)
+const void* k_convert(int dtype);           // convert_queries_kernel<T>(q, nq, dim, ld_out, metric, out)
+const void* k_rescore(int dtype);           // rescore_kernel<T>(X, ld, dim, q, nq, metric, flags, threshold, IdMap, kpad, keys)
+// merge.cuh, filter.cuh, rank.cuh
+const void* k_merge();                      // merge_topk_kernel(MergeParams)
+const void* k_finish(int dtype, int rows);  // finish_chunks_kernel<T, rows>(FinishParams)
+const void* k_filter_mark();                // filter_*_kernel(FilterParams[, n_ctas])
+const void* k_filter_cut();
+const void* k_filter_window();
+const void* k_ts_check();                   // rank.cuh
+const void* k_ts_fill();
+const void* k_rank_init();
+const void* k_rank_bitonic();
+const void* k_rank_scatter();
+// scan.cuh: scan_topk_kernel<T, G, CPL, U>(ScanParams); null when (G, cpl) has no instantiation
+const void* k_scan(int dtype, int G, int cpl, int* rows_per_warp_iter);
+const void* k_scan_generic(int dtype, int* rows_per_warp_iter);
+// ingest.cuh
+const void* k_norm_pack(int tin, int tout, int cpl);   // cpl 1..4: norm_pack_reg_kernel<Tin,Tout,cpl,1>; 0: norm_pack_kernel
+const void* k_pool(int tin, int tm, int tout);         // pool_norm_pack_kernel<Tin,Tm,Tout>
+int pool_threads();
+
+}  // namespace ragb

@@ -5,26 +5,11 @@
 // merges, the warps are tree-merged, warp 0 decodes keys to (score, id).
 #pragma once
 #include "common.cuh"
+#include "params.h"
 
 namespace ragb {
 
-constexpr int kMergeThreads = 256;
-constexpr int kMergeWarps = kMergeThreads / 32;
 
-struct MergeParams {
-  const uint64_t* keys;
-  int n_lists, kpad, k;
-  int unsorted;         // lists are unordered key bags (0 = empty) instead of sorted runs
-  int64_t stride_q, stride_p;
-  float* out_scores;    // [nq][k] or null
-  int64_t* out_ids;     // [nq][k] or null
-  uint64_t* out_keys;   // [nq][kpad] or null (sorted keys, for a later merge level)
-  PeerOut peers;        // peers.n > 0: the kpad sorted keys also go to every rank's gather buffer
-  const uint64_t* wait_flags;  // wait_n > 0: first wait until wait_flags[0..wait_n) have reached wait_epoch
-  int wait_n;
-  unsigned long long wait_epoch;
-  int* status;          // set to 1 when the wait timed out (a rank never arrived)
-};
 
 __global__ void __launch_bounds__(kMergeThreads) merge_topk_kernel(const MergeParams p) {
   extern __shared__ __align__(16) uint64_t smem_lists[];
@@ -59,7 +44,7 @@ __global__ void __launch_bounds__(kMergeThreads) merge_topk_kernel(const MergePa
     for (int i = lane; i < p.k; i += 32) {
       uint64_t key = tk.buf[i];
       if (p.out_scores) p.out_scores[qi * p.k + i] = key ? key_score(key) : -INFINITY;
-      if (p.out_ids) p.out_ids[qi * p.k + i] = key ? (int64_t)key_id(key) : -1;
+      if (p.out_ids) p.out_ids[qi * p.k + i] = key ? decode_id(p.row_of_id, key_id(key)) : -1;
     }
     if (p.out_keys)
       for (int i = lane; i < p.kpad; i += 32) p.out_keys[qi * p.kpad + i] = i < p.k ? tk.buf[i] : 0;
@@ -78,24 +63,6 @@ __global__ void __launch_bounds__(kMergeThreads) merge_topk_kernel(const MergePa
 //      what the reference applies per row (ollama_rag_system.py:480-508): row window, valid mask, clamp,
 //      `>= threshold`;
 //   3. keep the k best rows (:511-515), decode to (score, global id).
-struct FinishParams {
-  const uint64_t* parts;  // [nq][n_lists][kpad] sorted chunk keys
-  int n_lists, kpad, k_sel, k;
-  const void* X;          // packed rows
-  int64_t ld;
-  int dim;
-  const float* q;         // [nq][dim] fp32
-  int metric, flags;
-  float threshold;
-  int64_t row_begin, row_end;
-  const uint8_t* valid;
-  uint32_t id_base;
-  float* out_scores;      // [nq][k] or null
-  int64_t* out_ids;       // [nq][k] or null
-  uint64_t* out_keys;     // [nq][kpad] or null
-  PeerOut peers;          // peers.n > 0: the kpad sorted keys also go to every rank's gather buffer
-};
-constexpr int kFinishMaxChunkRows = 32;
 
 // number of keys of a descending-sorted list (zeros at the tail) that are greater than `key`
 __device__ __forceinline__ int count_greater_sorted(const uint64_t* list, int len_pow2, uint64_t key) {
@@ -105,10 +72,6 @@ __device__ __forceinline__ int count_greater_sorted(const uint64_t* list, int le
   return pos + (list[pos] > key ? 1 : 0);
 }
 
-// shared memory: lists [n_lists*kpad] | chunk [kpad] | cmax [kpad] | surv [kpad*32] | final [kpad] | misc
-__host__ __device__ inline size_t finish_smem_bytes(int n_lists, int kpad) {
-  return ((size_t)n_lists * kpad + (size_t)kpad * (3 + kFinishMaxChunkRows)) * sizeof(uint64_t) + 16;
-}
 
 // kRows = rows per chunk: 16 (a half-warp per chunk, two chunks per warp at a time) or 32 (a warp per chunk)
 template <typename T, int kRows>
@@ -259,7 +222,7 @@ __global__ void __launch_bounds__(kMergeThreads, 3) finish_chunks_kernel(const F
     const float sc = finish_score(mine, scale, p.flags);
     bool ok = active && row >= p.row_begin && row < p.row_end && sc >= p.threshold;
     if (ok && p.valid) ok = p.valid[row] != 0;
-    const uint64_t key = ok ? make_key(sc, (uint32_t)row + p.id_base) : 0ull;
+    const uint64_t key = ok ? make_key(sc, map_id(p.ids, row)) : 0ull;
     if (active) surv[c * kFinishChunkRows + (lane & kLaneMask)] = key;  // parked; filtered below
     uint64_t m = key;
 #pragma unroll
@@ -312,7 +275,7 @@ __global__ void __launch_bounds__(kMergeThreads, 3) finish_chunks_kernel(const F
   for (int i = threadIdx.x; i < p.k; i += kMergeThreads) {
     const uint64_t key = fin[i];
     if (p.out_scores) p.out_scores[qi * p.k + i] = key ? key_score(key) : -INFINITY;
-    if (p.out_ids) p.out_ids[qi * p.k + i] = key ? (int64_t)key_id(key) : -1;
+    if (p.out_ids) p.out_ids[qi * p.k + i] = key ? decode_id(p.row_of_id, key_id(key)) : -1;
   }
   if (p.out_keys)
     for (int i = threadIdx.x; i < p.kpad; i += kMergeThreads) p.out_keys[qi * p.kpad + i] = i < p.k ? fin[i] : 0;

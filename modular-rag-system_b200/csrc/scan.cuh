@@ -10,32 +10,11 @@
 // (merge.cuh) folds into the final k.
 #pragma once
 #include "common.cuh"
+#include "params.h"
 
 namespace ragb {
 
-constexpr int kScanThreads = 256;
-constexpr int kScanWarps = kScanThreads / 32;
 
-struct ScanParams {
-  const void* X;         // packed rows
-  int64_t ld;            // row stride, elements
-  int dim;
-  int64_t row_begin, row_end;
-  const uint8_t* valid;  // optional, indexed by absolute row
-  const float* q;        // [nq][ld_q] fp32
-  int64_t ld_q;
-  int metric, flags;
-  float threshold;
-  int k, kpad;
-  uint32_t id_base;
-  uint64_t* out;         // [nq][gridDim.x][kpad]
-  // fused final merge (the last CTA of a query to finish folds all per-CTA lists): null tickets = off
-  unsigned* tickets;     // [nq], zero before the launch; the merging CTA resets its entry
-  float* out_scores;     // [nq][k] or null
-  int64_t* out_ids;      // [nq][k] or null
-  uint64_t* out_keys;    // [nq][kpad] or null (sorted keys, for the cross-GPU merge)
-  PeerOut peers;         // peers.n > 0 (needs tickets): the merging CTA also stores the keys into every rank's buffer
-};
 
 __device__ __forceinline__ float query_scale(const float* q, int dim, int metric, int lane) {
   if (metric != 1) return 1.0f;
@@ -121,7 +100,7 @@ __device__ __forceinline__ void fused_final_merge(WarpTopK& tk, uint64_t* smem_l
       const uint64_t key = fin[i];
       if (i < p.k) {
         if (p.out_scores) p.out_scores[qi * p.k + i] = key ? key_score(key) : -INFINITY;
-        if (p.out_ids) p.out_ids[qi * p.k + i] = key ? (int64_t)key_id(key) : -1;
+        if (p.out_ids) p.out_ids[qi * p.k + i] = key ? decode_id(p.row_of_id, key_id(key)) : -1;
       }
       if (p.out_keys) p.out_keys[qi * p.kpad + i] = key;
       if (p.peers.n) peer_emit(p.peers, qi * p.kpad + i, key);
@@ -144,7 +123,7 @@ __device__ __forceinline__ void fused_final_merge(WarpTopK& tk, uint64_t* smem_l
       for (int i = lane; i < p.k; i += 32) {
         const uint64_t key = tk.buf[i];
         if (p.out_scores) p.out_scores[qi * p.k + i] = key ? key_score(key) : -INFINITY;
-        if (p.out_ids) p.out_ids[qi * p.k + i] = key ? (int64_t)key_id(key) : -1;
+        if (p.out_ids) p.out_ids[qi * p.k + i] = key ? decode_id(p.row_of_id, key_id(key)) : -1;
       }
       if (p.out_keys)
         for (int i = lane; i < p.kpad; i += 32) p.out_keys[qi * p.kpad + i] = i < p.k ? tk.buf[i] : 0;
@@ -224,7 +203,7 @@ __global__ void __launch_bounds__(kScanThreads, 2) scan_topk_kernel(const ScanPa
       const int64_t r = r0 + u * RPW;
       float s = finish_score(acc[u], scale, p.flags);
       bool ok = (gl == 0) && (r < p.row_end) && (s >= p.threshold);
-      uint64_t key = make_key(s, (uint32_t)r + p.id_base);
+      const uint64_t key = ok ? make_key(s, map_id(p.ids, r)) : 0ull;
       ok = ok && (key > tk.thr);
       if (ok && p.valid) ok = p.valid[r] != 0;
       tk.push(ok, key, lane);
@@ -288,7 +267,7 @@ __global__ void __launch_bounds__(kScanThreads, 2) scan_topk_generic_kernel(cons
       const int64_t r = r0 + u;
       float s = finish_score(acc[u], scale, p.flags);
       bool ok = (lane == 0) && (r < p.row_end) && (s >= p.threshold);
-      uint64_t key = make_key(s, (uint32_t)r + p.id_base);
+      const uint64_t key = ok ? make_key(s, map_id(p.ids, r)) : 0ull;
       ok = ok && (key > tk.thr);
       if (ok && p.valid) ok = p.valid[r] != 0;
       tk.push(ok, key, lane);

@@ -33,7 +33,7 @@ from typing import Any, Dict, Iterable, List, Optional, Sequence
 
 import numpy as np
 
-from .store import DeviceStore
+from .store import DeviceStore, ShardedDeviceStore
 
 NEG_INF = float("-inf")
 
@@ -115,8 +115,8 @@ class B200VectorStore:
     """Vector storage and retrieval for RAG with the embedding store on a B200 (see module docstring)."""
 
     def __init__(self, storage_path: Path, use_chromadb: bool = True, *, dtype: str = "fp16", device: int = 0,
-                 window: Optional[int] = 1000, capacity: int = 4096, embedding_generator=None,
-                 result_types=None):
+                 devices: Optional[Sequence[int]] = None, window: Optional[int] = 1000, capacity: int = 4096,
+                 embedding_generator=None, result_types=None):
         self.storage_path = Path(storage_path)
         self.storage_path.mkdir(parents=True, exist_ok=True)
         self.use_chromadb = False            # the exact path is the SQLite + device path (SURVEY D7)
@@ -124,7 +124,9 @@ class B200VectorStore:
         self.faiss_index = None              # the device store takes this slot (:242, :298-305)
         self.document_mapping: Dict[int, str] = {}   # device row -> doc id (:243, :383)
         self.window = window
-        self.dtype, self.device = dtype, int(device)
+        # devices=[0, 1, ...]: the rows are sharded over these GPUs (ShardedDeviceStore); else one GPU (`device`)
+        self.devices = [int(d) for d in devices] if devices else [int(device)]
+        self.dtype, self.device = dtype, self.devices[0]
         self._capacity0 = int(capacity)
         self._types = result_types or (RAGDocument, RAGResult)
         self._lock = threading.RLock()
@@ -136,11 +138,14 @@ class B200VectorStore:
         self._has = np.zeros(0, bool)                 # False for NULL embeddings (:485-492)
         self._row_of: Dict[str, int] = {}
         self._src_code: Dict[str, int] = {}
-        self._monotone = True                         # timestamps non-decreasing in row order
-        self._device_filter = True                    # candidate-set policy evaluated on the device (filter.cuh)
         self._meta_version = 0
         self._filter_key = None                       # (meta version, sources, window) of the mask now in the store
         self._filter_total = 0
+        # searches run outside the lock (the GUI spawns a thread per query, rag_query_interface.py:740-744): readers
+        # of the current device mask are counted; whoever needs another mask, or appends, waits until they are out
+        self._cv = threading.Condition(self._lock)
+        self._readers = 0
+        self._writers_waiting = 0
         self._init_sqlite_fallback()
         self.restored_from = "sqlite"                 # "sidecar" when the packed rows came back from disk
         if not self._load_sidecar():
@@ -206,7 +211,7 @@ class B200VectorStore:
                 np.savez(p_meta, ids=np.array([self.document_mapping[r] for r in range(n)], dtype=np.str_),
                          ts=self._ts[:n], src=self._src[:n], live=self._live[:n], has=self._has[:n],
                          src_names=np.array(names, dtype=np.str_), dtype=np.array(self.dtype), dim=np.array(self._store.dim),
-                         monotone=np.array(self._monotone), fingerprint=np.array(self._fingerprint()))
+                         fingerprint=np.array(self._fingerprint()))
             return True
         except Exception as e:
             print(f"Sidecar save error: {e}")
@@ -226,7 +231,7 @@ class B200VectorStore:
             if n != len(meta["ids"]) or n != len(norms) or dim != int(meta["dim"]):
                 return False
             with self._lock:
-                self._store = DeviceStore(dim, self.dtype, max(self._capacity0, n), self.device)
+                self._store = self._new_store(dim, max(self._capacity0, n))
                 for r0 in range(0, n, 262144):  # slabs: the memory-mapped file never sits in RAM as a whole
                     r1 = min(n, r0 + 262144)
                     self._store.put_rows(np.ascontiguousarray(rows[r0:r1]), norms[r0:r1])
@@ -237,7 +242,6 @@ class B200VectorStore:
                 ids = meta["ids"].tolist()
                 self.document_mapping = dict(enumerate(ids))
                 self._row_of = {d: r for r, d in enumerate(ids) if self._live[r]}
-                self._monotone = bool(meta["monotone"])
                 self._n = n
                 self._meta_version += 1
                 self._push_meta(0, n, [])
@@ -251,6 +255,11 @@ class B200VectorStore:
                 self._store, self._n = None, 0
                 self.document_mapping, self._row_of, self._src_code = {}, {}, {}
             return False
+
+    def _new_store(self, dim: int, capacity: int):
+        if len(self.devices) > 1:
+            return ShardedDeviceStore(dim, self.dtype, capacity, self.devices)
+        return DeviceStore(dim, self.dtype, capacity, self.device)
 
     # -- host-side row table ------------------------------------------------------------------ #
     def _grow_meta(self, need: int):
@@ -267,6 +276,12 @@ class B200VectorStore:
         """items: (doc_id, embedding-or-None, timestamp, source).  One device row per item; NULL and
         wrong-length embeddings become zero rows (they score 0.0, :201-202 / :214-215)."""
         with self._lock:
+            self._writers_waiting += 1
+            try:
+                while self._readers > 0:       # a search in flight reads the mask / metadata this append rewrites
+                    self._cv.wait()
+            finally:
+                self._writers_waiting -= 1
             dim = None if self._store is None else self._store.dim
             if dim is None:
                 for _, emb, _, _ in items:
@@ -275,14 +290,14 @@ class B200VectorStore:
                         break
                 if dim is None:
                     dim = 1  # only NULL embeddings so far; re-created when the first real vector arrives
-                self._store = DeviceStore(dim, self.dtype, max(self._capacity0, len(items)), self.device)
+                self._store = self._new_store(dim, max(self._capacity0, len(items)))
                 self._dim_is_placeholder = all(e is None or len(e) == 0 for _, e, _, _ in items)
             elif getattr(self, "_dim_is_placeholder", False):
                 real = next((len(e) for _, e, _, _ in items if e is not None and len(e) > 0), None)
                 if real is not None:  # every earlier row is a NULL row: rebuild them as zero rows
                     n_old = self._n
                     self._store.close()
-                    self._store = DeviceStore(real, self.dtype, max(self._capacity0, n_old + len(items)), self.device)
+                    self._store = self._new_store(real, max(self._capacity0, n_old + len(items)))
                     if n_old:
                         self._store.add(np.zeros((n_old, real), np.float32))
                         self._push_meta(0, n_old, [])
@@ -308,25 +323,26 @@ class B200VectorStore:
                     replaced.append(old)
                 self._row_of[doc_id] = r
                 self.document_mapping[r] = doc_id
-                t = float(ts) if ts is not None else 0.0
-                if r > 0 and t < self._ts[r - 1]:
-                    self._monotone = False
-                self._ts[r] = t
+                self._ts[r] = float(ts) if ts is not None else 0.0
                 self._src[r] = self._src_code.setdefault(source, len(self._src_code))
                 self._live[r] = True
                 self._has[r] = has[i]
             self._n += len(items)
             self._meta_version += 1
             self._push_meta(first, len(items), replaced)
+            self._cv.notify_all()
 
     def _push_meta(self, first: int, m: int, replaced: Sequence[int]) -> None:
-        """Mirror live / has-embedding / source of the new rows (and the rows they replaced) onto the device, where
-        the candidate-set policy is evaluated (csrc/filter.cuh)."""
-        if len(self._src_code) > 65535:
-            self._device_filter = False  # more sources than 16-bit codes: host-built masks from here on
+        """Mirror live / has-embedding / source / timestamp of the new rows (and the rows they replaced) onto the
+        device, where the candidate-set policy is evaluated (csrc/filter.cuh, csrc/rank.cuh): nothing about the
+        candidate set is computed on the host."""
+        if len(self._src_code) > 65536:
+            raise ValueError("more than 65536 distinct sources: the device filter carries 16-bit source codes")
+        if m == 0:
             return
         flags = self._live[first:first + m].astype(np.uint8) | (self._has[first:first + m].astype(np.uint8) << 1)
         self._store.set_meta(first, flags, self._src[first:first + m].astype(np.uint16))
+        self._store.set_timestamps(first, self._ts[first:first + m])
         for r in replaced:
             if r < first:
                 self._store.set_meta(r, np.array([int(self._has[r]) << 1], np.uint8))
@@ -381,26 +397,6 @@ class B200VectorStore:
         return ok
 
     # -- retrieve (:388-403, :454-525) -------------------------------------------------------- #
-    def _candidate_rows(self, source_filters):
-        """(valid mask over device rows, rows the SQL query of :462-477 would return)."""
-        n = self._n
-        m = self._live[:n].copy()
-        if source_filters:
-            codes = [self._src_code[s] for s in source_filters if s in self._src_code]
-            m &= np.isin(self._src[:n], codes)
-        total = int(m.sum())
-        if self.window is not None and total > self.window:
-            rows = np.flatnonzero(m)
-            if self._monotone:
-                keep = rows[-self.window:]
-            else:  # newest `window` by timestamp; later row wins a timestamp tie
-                order = np.lexsort((rows, self._ts[rows]))
-                keep = rows[order[-self.window:]]
-            m = np.zeros(n, bool)
-            m[keep] = True
-            total = self.window
-        return m & self._has[:n], total
-
     def search(self, query) -> Any:
         """Exact top-``max_results`` of the stored documents for ``query`` (a ``RAGQuery``)."""
         Doc, Res = self._types
@@ -416,8 +412,9 @@ class B200VectorStore:
         return results
 
     def _device_candidates(self, source_filters) -> int:
-        """Monotone timestamps: the SQL's WHERE / ORDER BY / LIMIT (:462-477) evaluated by kernels into the store's
-        own mask; returns total_documents_searched.  Cached until rows, metadata or the filter change."""
+        """The SQL's WHERE / ORDER BY timestamp DESC / LIMIT (:462-477) evaluated by kernels into the store's own mask;
+        returns total_documents_searched.  Cached until rows, metadata or the filter change.  Caller holds the lock
+        and has waited until no search reads the current mask."""
         srcs = tuple(sorted(set(source_filters))) if source_filters else None
         key = (self._meta_version, srcs, self.window)
         if key != self._filter_key:
@@ -431,48 +428,35 @@ class B200VectorStore:
             self._filter_key = key
         return self._filter_total
 
-    def _search_rows(self, Q: np.ndarray, k: int, thr: float, source_filters):
-        """Device search of host queries Q [nq, dim] under the reference's policy -> (ids [nq][<=k], scores, total)."""
+    def _search_rows(self, Q: Optional[np.ndarray], k: int, thr: float, source_filters):
+        """Device search of host queries Q [nq, dim] under the reference's policy -> (ids [nq][<=k], scores, total).
+        The lock is held only to pick (or rebuild) the device mask; the search itself runs outside it, so reader
+        threads overlap (per-call stream + workspace inside the C ABI).  Q = None: only the candidate count."""
+        srcs = tuple(sorted(set(source_filters))) if source_filters else None
         with self._lock:
             n, store = self._n, self._store
             if store is None or n == 0:
                 return None, None, 0
-            monotone = self._monotone
-            if monotone and self._device_filter:
-                total = self._device_candidates(source_filters)
-                if total == 0 or k <= 0:
-                    return None, None, total
-                ids, sc = store.search(Q, min(k, 1024), "cosine", threshold=thr, clamp01=True, row_end=n, valid="filter")
-                return ids, sc, total
-            valid, total = self._candidate_rows(source_filters)
-            ts = self._ts[:n].copy() if not monotone else None
-        if k <= 0 or not valid.any():
-            return None, None, total
-        n_valid = int(valid.sum())
-        kk = min(k, 1024)
-        v8 = valid.astype(np.uint8)
-        while True:
-            ids, sc = store.search(Q, kk, "cosine", threshold=thr, clamp01=True, row_end=n, valid=v8)
-            full = (ids[:, kk - 1] >= 0) & (sc[:, kk - 1] >= sc[:, min(k, kk) - 1])
-            if monotone or kk >= min(n_valid, 1024) or not full.any():
-                break  # the tie group at the cut is complete for every query (or timestamps follow row order)
-            kk = min(1024, 2 * kk)
-        if not monotone:  # reference order: score desc, then newer timestamp (:474, :512)
-            out_i, out_s = np.full((len(ids), k), -1, np.int64), np.full((len(ids), k), -np.inf, np.float32)
-            for j in range(len(ids)):
-                g = ids[j] >= 0
-                ij, sj = ids[j][g], sc[j][g]
-                order = np.lexsort((-ij, -ts[ij], -sj.astype(np.float64)))[:k]
-                out_i[j, :len(order)], out_s[j, :len(order)] = ij[order], sj[order]
-            ids, sc = out_i, out_s
-        return ids[:, :k], sc[:, :k], total
+            key = (self._meta_version, srcs, self.window)
+            while self._writers_waiting > 0 or (self._filter_key != key and self._readers > 0):
+                self._cv.wait()
+            total = self._device_candidates(source_filters)
+            if Q is None or total == 0 or k <= 0:
+                return None, None, total
+            self._readers += 1
+        try:
+            ids, sc = store.search(Q, min(k, 1024), "cosine", threshold=thr, clamp01=True, row_end=n, valid="filter")
+        finally:
+            with self._lock:
+                self._readers -= 1
+                self._cv.notify_all()
+        return ids, sc, total
 
     def _search_device(self, query, query_embedding):
         Doc, Res = self._types
         k = int(query.max_results)
         if not query_embedding:  # :493 — nothing is scored without a query vector
-            with self._lock:
-                total = 0 if self._store is None or self._n == 0 else self._candidate_rows(query.source_filters)[1]
+            total = self._search_rows(None, k, 0.0, query.source_filters)[2]
             return Res(documents=[], similarities=[], total_documents_searched=total)
         q = np.asarray(query_embedding, dtype=np.float32)[None, :]
         ids, sc, total = self._search_rows(q, k, float(query.similarity_threshold), query.source_filters)
@@ -560,7 +544,8 @@ class B200VectorStore:
     def get_stats(self) -> Dict[str, Any]:
         stats = {'backend': 'b200+sqlite', 'total_documents': 0, 'sources': {},
                  'embedding_cache_size': len(getattr(self.embedding_generator, 'embedding_cache', {})),
-                 'device_rows': self._n, 'dtype': self.dtype, 'gpus': 1, 'device': self.device,
+                 'device_rows': self._n, 'dtype': self.dtype, 'gpus': len(self.devices), 'device': self.device,
+                 'devices': list(self.devices),
                  'dim': None if self._store is None else self._store.dim}
         try:
             with sqlite3.connect(self.db_path) as conn:

@@ -179,6 +179,7 @@ class ShardedSearcher:
         if getattr(self, "_qpin", None) is None or self._qpin.shape != q.shape:
             self._qpin = torch.empty(q.shape, dtype=torch.float32, pin_memory=True)
             self._qdev = torch.empty(q.shape, dtype=torch.float32, device=dev)
+        if getattr(self, "_ipin", None) is None or self._ipin.shape != (q.shape[0], k):   # outputs are [nq, k]: keyed on k too
             self._ipin = torch.empty((q.shape[0], k), dtype=torch.int64, pin_memory=True)
             self._spin = torch.empty((q.shape[0], k), dtype=torch.float32, pin_memory=True)
         self._qpin.numpy()[...] = q

@@ -264,6 +264,13 @@ class DeviceStore:
         check(self._lib.ragb_store_set_meta(self._h, int(row0), int(n), None if f is None else f.ctypes.data,
                                             None if c is None else c.ctypes.data))
 
+    def set_timestamps(self, row0: int, ts: np.ndarray) -> None:
+        """Per-row timestamps (RAGDocument.timestamp): the order "ORDER BY timestamp DESC" (ollama_rag_system.py:474)
+        and the stable sort (:512) rank by.  Out-of-order timestamps make the store build recency ranks on the device
+        (csrc/rank.cuh); nothing changes while they follow row order."""
+        t = np.ascontiguousarray(ts, dtype=np.float64)
+        check(self._lib.ragb_store_set_timestamps(self._h, int(row0), int(len(t)), t.ctypes.data))
+
     def build_filter(self, allowed_sources: Optional[np.ndarray] = None, window: Optional[int] = None) -> int:
         """Evaluate (source IN ..., newest `window` rows, live, non-NULL) on the device into the store's own mask;
         returns the number of rows the reference's SQL would have returned.  Search with ``valid="filter"``."""
@@ -290,6 +297,175 @@ class DeviceStore:
         """(summed kernel milliseconds, bracketed launches) since the last read; waits for the events."""
         ms, n = C.c_double(0.0), C.c_int64(0)
         check(self._lib.ragb_store_profile_read(self._h, C.byref(ms), C.byref(n)))
+        return ms.value, n.value
+
+
+class ShardedDeviceStore:
+    """The row-sharded store (include/ragb200.h: ragb_mstore_*): ONE process, rows dealt over several GPUs of one
+    NVSwitch box in blocks, round-robin; the last kernel of every shard stores its k candidates per query into the
+    first device's gather buffer over NVLink (peer memory), one merge kernel finishes.  Same host interface as
+    ``DeviceStore`` for everything ``B200VectorStore`` uses; results are identical to the one-device store's."""
+
+    def __init__(self, dim: int, dtype: str = "fp16", capacity: int = 1 << 16, devices=(0,), block_rows: int = 0):
+        self._h = C.c_void_p()
+        self._lib = lib()
+        code = _DTYPES[dtype] if isinstance(dtype, str) else int(dtype)
+        devs = (C.c_int * len(devices))(*[int(d) for d in devices])
+        check(self._lib.ragb_mstore_create(int(dim), code, int(capacity), devs, len(devices), int(block_rows), C.byref(self._h)))
+        self.dim, self.dtype_code, self.devices = int(dim), code, [int(d) for d in devices]
+        self.device = self.devices[0]
+
+    def close(self) -> None:
+        if getattr(self, "_h", None) is not None and self._h.value:
+            self._lib.ragb_mstore_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __len__(self) -> int:
+        return int(self._lib.ragb_mstore_size(self._h))
+
+    @property
+    def capacity(self) -> int:
+        return int(self._lib.ragb_mstore_capacity(self._h))
+
+    @property
+    def block_rows(self) -> int:
+        return int(self._lib.ragb_mstore_block_rows(self._h))
+
+    @property
+    def dtype(self) -> str:
+        return {F16: "fp16", BF16: "bf16", F32: "fp32"}[self.dtype_code]
+
+    def device_rows(self) -> list:
+        return [int(self._lib.ragb_mstore_device_rows(self._h, i)) for i in range(len(self.devices))]
+
+    def reserve(self, capacity: int) -> None:
+        check(self._lib.ragb_mstore_reserve(self._h, int(capacity)))
+
+    def clear(self) -> None:
+        check(self._lib.ragb_mstore_clear(self._h))
+
+    def _room(self, n: int) -> None:
+        need = len(self) + n
+        if need > self.capacity:
+            self.reserve(max(need, 2 * self.capacity, 1024))
+
+    def add(self, rows: np.ndarray) -> int:
+        rows = np.ascontiguousarray(np.atleast_2d(rows), dtype=np.float32)
+        if rows.shape[1] != self.dim:
+            raise ValueError(f"rows have dim {rows.shape[1]}, store has {self.dim}")
+        self._room(rows.shape[0])
+        first = C.c_int64(-1)
+        check(self._lib.ragb_mstore_add(self._h, rows.ctypes.data, rows.shape[0], C.byref(first)))
+        return first.value
+
+    def add_dev(self, rows) -> int:
+        """torch CUDA tensor [n, dim] on ANY device of the box: every shard's ingest kernel reads its blocks in place."""
+        if rows.dim() != 2 or rows.shape[1] != self.dim or rows.stride(1) != 1:
+            raise ValueError("expected a [n, dim] tensor with unit inner stride")
+        self._room(rows.shape[0])
+        first = C.c_int64(-1)
+        check(self._lib.ragb_mstore_add_dev(self._h, rows.data_ptr(), _torch_code(rows), rows.shape[0], rows.stride(0),
+                                            C.byref(first), _cur_stream(rows.device.index or 0)))
+        return first.value
+
+    def set(self, row: int, vec: np.ndarray) -> None:
+        vec = np.ascontiguousarray(vec, dtype=np.float32).reshape(-1)
+        if vec.shape[0] != self.dim:
+            raise ValueError("dimension mismatch")
+        check(self._lib.ragb_mstore_set(self._h, int(row), vec.ctypes.data))
+
+    def get_rows(self, row0: int = 0, n: Optional[int] = None) -> Tuple[np.ndarray, np.ndarray]:
+        n = len(self) - row0 if n is None else n
+        rows = np.empty((n, self.dim), dtype=_np_elem(self.dtype_code))
+        norms = np.empty(n, dtype=np.float32)
+        check(self._lib.ragb_mstore_get_rows(self._h, int(row0), int(n), rows.ctypes.data, norms.ctypes.data))
+        return rows, norms
+
+    def put_rows(self, rows: np.ndarray, norms: np.ndarray) -> int:
+        rows = np.ascontiguousarray(rows, dtype=_np_elem(self.dtype_code))
+        norms = np.ascontiguousarray(norms, dtype=np.float32)
+        if rows.ndim != 2 or rows.shape[1] != self.dim or norms.shape[0] != rows.shape[0]:
+            raise ValueError("expected packed rows [n, dim] and norms [n]")
+        self._room(rows.shape[0])
+        first = C.c_int64(-1)
+        check(self._lib.ragb_mstore_put_rows(self._h, rows.ctypes.data, norms.ctypes.data, rows.shape[0], C.byref(first)))
+        return first.value
+
+    def set_meta(self, row0: int, flags: Optional[np.ndarray] = None, src: Optional[np.ndarray] = None) -> None:
+        n = len(flags) if flags is not None else len(src)
+        f = None if flags is None else np.ascontiguousarray(flags, dtype=np.uint8)
+        c = None if src is None else np.ascontiguousarray(src, dtype=np.uint16)
+        check(self._lib.ragb_mstore_set_meta(self._h, int(row0), int(n), None if f is None else f.ctypes.data,
+                                             None if c is None else c.ctypes.data))
+
+    def set_timestamps(self, row0: int, ts: np.ndarray) -> None:
+        t = np.ascontiguousarray(ts, dtype=np.float64)
+        check(self._lib.ragb_mstore_set_timestamps(self._h, int(row0), int(len(t)), t.ctypes.data))
+
+    def build_filter(self, allowed_sources: Optional[np.ndarray] = None, window: Optional[int] = None) -> int:
+        tot = C.c_int64(0)
+        a = None if allowed_sources is None else np.ascontiguousarray(allowed_sources, dtype=np.uint8)
+        check(self._lib.ragb_mstore_build_filter(self._h, None if a is None else a.ctypes.data, 0 if a is None else len(a),
+                                                 -1 if window is None else int(window), C.byref(tot)))
+        return int(tot.value)
+
+    def search(self, q: np.ndarray, k: int, metric: str = "ip", threshold: float = NEG_INF, clamp01: bool = False,
+               row_begin: int = 0, row_end: int = -1, valid=None, flags: int = 0) -> Tuple[np.ndarray, np.ndarray]:
+        if row_begin != 0 or (row_end >= 0 and row_end != len(self)):
+            raise ValueError("the sharded store searches all rows: restrict with a valid mask or build_filter")
+        q = np.ascontiguousarray(np.atleast_2d(q), dtype=np.float32)
+        nq = q.shape[0]
+        if q.shape[1] != self.dim:
+            q = np.zeros((nq, self.dim), dtype=np.float32)
+        ids = np.empty((nq, k), dtype=np.int64)
+        scores = np.empty((nq, k), dtype=np.float32)
+        vp = None
+        if isinstance(valid, str):
+            if valid != "filter":
+                raise ValueError('valid must be a byte mask or the string "filter"')
+            vp = _lib.STORE_FILTER
+        elif valid is not None:
+            valid = np.ascontiguousarray(valid, dtype=np.uint8)
+            if valid.shape[0] < len(self):
+                raise ValueError("valid mask shorter than the store")
+            vp = valid.ctypes.data
+        fl = int(flags) | (CLAMP01 if clamp01 else 0)
+        check(self._lib.ragb_mstore_search(self._h, q.ctypes.data, nq, int(k), _METRICS[metric], float(threshold), fl, vp,
+                                           scores.ctypes.data, ids.ctypes.data))
+        return ids, scores
+
+    def search_dev(self, q, k: int, metric: str = "ip", threshold: float = NEG_INF, clamp01: bool = False, valid=None,
+                   flags: int = 0, out=None):
+        """torch CUDA fp32 queries [nq, dim] on the FIRST device -> (ids, scores) there, on its current stream."""
+        import torch
+        if q.dtype != torch.float32 or q.dim() != 2 or q.shape[1] != self.dim or not q.is_contiguous():
+            raise ValueError(f"queries must be contiguous fp32 [nq,{self.dim}]")
+        if (q.device.index or 0) != self.devices[0]:
+            raise ValueError(f"queries must live on the store's first device (cuda:{self.devices[0]})")
+        nq = q.shape[0]
+        if out is None:
+            ids = torch.empty((nq, k), dtype=torch.int64, device=q.device)
+            scores = torch.empty((nq, k), dtype=torch.float32, device=q.device)
+        else:
+            ids, scores = out
+        fl = int(flags) | (CLAMP01 if clamp01 else 0)
+        check(self._lib.ragb_mstore_search_dev(self._h, q.data_ptr(), nq, int(k), _METRICS[metric], float(threshold), fl,
+                                               None if valid is None else _lib.STORE_FILTER, scores.data_ptr(), ids.data_ptr(),
+                                               _cur_stream(self.devices[0])))
+        return ids, scores
+
+    def profile(self, enable: bool = True) -> None:
+        check(self._lib.ragb_mstore_profile(self._h, 1 if enable else 0))
+
+    def profile_read(self) -> Tuple[float, int]:
+        ms, n = C.c_double(0.0), C.c_int64(0)
+        check(self._lib.ragb_mstore_profile_read(self._h, C.byref(ms), C.byref(n)))
         return ms.value, n.value
 
 

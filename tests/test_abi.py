@@ -26,7 +26,7 @@ def test_library_exports_every_symbol():
     l = ctypes.CDLL(str(_lib.LIB_PATH))
     for name in _declared():
         assert hasattr(l, name), name
-    assert _lib.lib().ragb_abi_version() == 1
+    assert _lib.lib().ragb_abi_version() == _lib.ABI_VERSION == 2
     assert _lib.lib().ragb_kpad(10) == 16 and _lib.lib().ragb_kpad(100) == 128
 
 

@@ -242,3 +242,62 @@ def test_sidecar_restores_bit_exact_and_yields_to_the_table(tmp_path):
     res = vs3.search(q)
     assert res.documents[0].id == "new" and res.documents[1].id == "d7"  # equal cosine 1.0: newer first
     vs3.close(save=False)
+
+
+def test_out_of_order_timestamps_on_the_device():
+    """ragb_store_set_timestamps: the newest-`window` cut and the order among equal scores follow the TIMESTAMP
+    (ollama_rag_system.py:474, :512), evaluated on the device (csrc/rank.cuh: recency ranks) — against the same policy
+    written in numpy.  Later row wins a timestamp tie; rows without a timestamp count as the newest, in row order."""
+    from modular_rag_system_b200 import DeviceStore
+    rng = np.random.default_rng(17)
+    n, d = 9_000, 64
+    X = rng.standard_normal((n, d)).astype(np.float32)
+    X[100] = X[7000] = X[8999] = X[4]          # four identical rows: equal scores for every query
+    s = DeviceStore(d, "fp16", n + 64)
+    s.add(X)
+    ts = rng.permutation(n).astype(np.float64)  # thoroughly out of order
+    ts[200:260] = ts[200]                       # a run of equal timestamps
+    ts[4], ts[100], ts[7000], ts[8999] = 5e6, 7e6, 6e6, 6e6
+    s.set_timestamps(0, ts)
+    live = rng.random(n) > 0.1
+    has = rng.random(n) > 0.05
+    live[[4, 100, 7000, 8999]] = has[[4, 100, 7000, 8999]] = True
+    src = rng.integers(0, 5, n).astype(np.uint16)
+    s.set_meta(0, live.astype(np.uint8) | (has.astype(np.uint8) << 1), src)
+    rank = np.empty(n, np.int64)
+    rank[np.lexsort((np.arange(n), ts))] = np.arange(n)
+    Q = rng.standard_normal((5, d)).astype(np.float32)
+    Q[0] = X[4]
+    for allowed_codes, window in ((None, None), (None, 1000), ([1, 3], 500), ([2], 7), (None, 2048), (None, 5000)):
+        allowed = None
+        match = live.copy()
+        if allowed_codes is not None:
+            allowed = np.zeros(5, np.uint8); allowed[allowed_codes] = 1
+            match &= np.isin(src, allowed_codes)
+        total = int(match.sum())
+        if window is not None and total > window:
+            rows = np.flatnonzero(match)
+            keep = rows[np.argsort(rank[rows])[total - window:]]
+            match = np.zeros(n, bool); match[keep] = True
+            total = window
+        assert s.build_filter(allowed, window) == total, (allowed_codes, window)
+        want = (match & has).astype(np.uint8)
+        a = s.search(Q, 10, "cosine", valid="filter")
+        b = s.search(Q, 10, "cosine", valid=want)
+        assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1]), (allowed_codes, window)
+    # equal scores: newest timestamp first, the later row among equal timestamps — on every kernel path
+    from modular_rag_system_b200._lib import FORCE_GEMM, FORCE_SCAN
+    for fl in (FORCE_SCAN, FORCE_GEMM, 0):
+        ids, sc = s.search(np.repeat(Q[:1], 6 if fl == 0 else 1, axis=0), 4, "cosine", flags=fl)
+        assert ids[0].tolist() == [100, 8999, 7000, 4], (fl, ids[0])
+    ids, _ = s.search(np.repeat(Q[:1], 200, axis=0), 4, "cosine")          # SM-pair kernel + finish
+    assert (ids == np.array([100, 8999, 7000, 4])).all()
+    # rows appended afterwards without a timestamp are the newest
+    s.add(X[4:5])
+    ids, _ = s.search(Q[:1], 5, "cosine")
+    assert ids[0].tolist() == [n, 100, 8999, 7000, 4]
+    # back in order: ranks are dropped again (identity)
+    s.set_timestamps(0, np.arange(n + 1, dtype=np.float64))
+    ids, _ = s.search(Q[:1], 5, "cosine")
+    assert ids[0].tolist() == [n, 8999, 7000, 100, 4]
+    s.close()
