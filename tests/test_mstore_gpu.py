@@ -52,7 +52,7 @@ def test_sharded_store_equals_single_store(dtype):
         r2, n2 = ms.get_rows()
         assert np.array_equal(r1.view(np.uint16), r2.view(np.uint16)) and np.array_equal(n1, n2)
         for nq, k, kw in ((1, 10, {}), (3, 5, dict(threshold=0.1, clamp01=True)), (40, 10, {}), (300, 10, {}),
-                          (300, 100, {}), (130, 32, dict(threshold=0.0, clamp01=True)), (2, 10, dict(flags=FORCE_SCAN))):
+                          (300, 100, {}), (130, 30, dict(threshold=0.0, clamp01=True)), (2, 10, dict(flags=FORCE_SCAN))):
             a = one.search(Q[:nq], k, "cosine", **kw)
             b = ms.search(Q[:nq], k, "cosine", **kw)
             assert np.array_equal(a[0], b[0]), (devs, nq, k, kw)
