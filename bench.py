@@ -572,10 +572,11 @@ def run_b200(args):
 
 
 def run_extras(args, pkg, torch, store, wl, pk, pk_src):
-    """Secondary cases of the metric on one GPU: batch 1 on the same corpus, and the other named corpus."""
+    """Secondary cases of the metric on one GPU: batch 1 on the same corpus, the other cells of BASELINE.json's metric
+    (1M/10M x 384/768, batch 1 & 1024), a small batch, one GPU's share of configs[4], ingest, the latency case."""
     out = []
 
-    def case(st, w, name, B, k=None, steps=None):
+    def case(st, w, name, B, k=None, steps=None, parity=False):
         k = k or args.k
         g = torch.Generator(device="cuda").manual_seed(2)
         Q = torch.randn((B, w["d"]), generator=g, device="cuda")
@@ -586,33 +587,66 @@ def run_extras(args, pkg, torch, store, wl, pk, pk_src):
         tensor = bound_of(B, pk) == "tensor"
         work = 2.0 * B * len(st) * w["d"] if tensor else float(len(st)) * w["d"] * 2
         roof = roofline_obj("tensor" if tensor else "hbm", st, work, pk, pk_src, sustained=False)
-        lps = max(1.0, roof["launches_timed"] / float(steps))  # a large top-100 batch runs as several launches of the kernel
-        roof["achieved"] /= lps
-        roof["frac"] /= lps
-        roof["launches_per_step"] = lps
-        roof["kernel_share_of_step"] = roof["kernel_ms"] * lps / (ms / steps)
+        per_step(roof, steps, ms)  # a large top-100 batch runs as several launches of the kernel
         attach_traffic(roof, f"{name}_b{B}_n1" if k == args.k else f"{name}_b{B}_k{k}_n1")
-        out.append({"workload": f"{name} batch {B}" + ("" if k == args.k else f" top-{k}"), "value": B * steps / (ms / 1e3),
-                    "unit": "queries/s", "ms_per_step": ms / steps, "roofline": roof})
+        row = {"workload": f"{name} batch {B}" + ("" if k == args.k else f" top-{k}"), "value": B * steps / (ms / 1e3),
+               "unit": "queries/s", "ms_per_step": ms / steps, "roofline": roof}
+        if parity and not args.no_parity:
+            par = parity_obj(torch, st, Q, k, w["dtype"])
+            row.update(recall_at_k=par["recall_at_k"], max_abs_score_err=par["max_abs_score_err"],
+                       parity_queries=par["parity_queries"], parity=par)
+        out.append(row)
 
     out.append(ingest_case(pkg, torch, pk, pk_src, store.device))
     out.append(latency_case(pkg, torch, store.device))
     case(store, wl, args.workload, 1 if args.batch != 1 else 1024)
-    other = "1Mx384" if args.workload != "1Mx384" else None
-    if other:
-        w2 = WORKLOADS[other]
-        st2 = fill_store(pkg, torch, w2, 0, w2["n"], store.device)
-        case(st2, w2, other, 1024)
-        case(st2, w2, other, 1)
-        st2.close()
     if args.workload == "10Mx768" and args.k == 10:
+        store.close()  # 15.4 GB back before the other corpora are filled; the headline numbers are already taken
+        for other in ("1Mx384", "1Mx768", "10Mx384"):
+            w2 = WORKLOADS[other]
+            st2 = fill_store(pkg, torch, w2, 0, w2["n"], store.device)
+            case(st2, w2, other, 1024, parity=(other == "1Mx384"))
+            case(st2, w2, other, 1)
+            if other == "1Mx384":
+                case(st2, w2, other, 128)   # one query tile: the pair kernel beside an all-zero tile
+            st2.close()
         # one GPU's share of BASELINE configs[4] (100M x 384 bf16, top-100, batch 4096 over 8 GPUs)
-        store.close()  # 15.4 GB back before 9.6 GB more are filled; the headline numbers are already taken
         w3 = dict(n=12_500_000, d=384, dtype="bf16")
         st3 = fill_store(pkg, torch, w3, 0, w3["n"], store.device)
-        case(st3, w3, "12.5Mx384 bf16", 4096, k=100, steps=5)
+        case(st3, w3, "12.5Mx384 bf16", 4096, k=100, steps=5, parity=True)
         st3.close()
     return out
+
+
+def run_extras_sharded(args, pkg, torch, dist, searcher, store, wl, pk, pk_src, world, rank, local):
+    """N > 1 (every rank takes part; rank 0 reports): batch 1 on the sharded headline corpus, and BASELINE configs[4]'s
+    shape per GPU (12.5M x 384 bf16 rows on every rank = 100M rows at 8 GPUs, top-100, batch 4096)."""
+    out = []
+
+    def case(srch, st, rows_total, w, name, B, k, steps):
+        g = torch.Generator(device="cuda").manual_seed(2)
+        Q = torch.randn((B, w["d"]), generator=g, device="cuda")
+        Q = (Q / Q.norm(dim=1, keepdim=True)).contiguous()
+        srch.search_dev(Q, k, "ip")   # exchange buffers for this (B, k): outside the timed region
+        torch.cuda.synchronize()
+        fn = (lambda: srch.search_dev(Q, k, "ip"))
+        ms = time_device(torch, dist, fn, steps, args.warmup, world, after_warmup=lambda: st.profile(True))
+        tensor = bound_of(B, pk) == "tensor"
+        work = 2.0 * B * len(st) * w["d"] if tensor else float(len(st)) * w["d"] * 2
+        roof = roofline_obj("tensor" if tensor else "hbm", st, work, pk, pk_src, sustained=False)
+        per_step(roof, steps, ms)
+        out.append({"workload": f"{name}, {rows_total} rows over {world} GPUs, batch {B}, top-{k}", "value": B * steps / (ms / 1e3),
+                    "unit": "queries/s", "ms_per_step": ms / steps, "n_gpus": world, "roofline": roof})
+
+    case(searcher, store, wl["n"], wl, args.workload, 1, args.k, 50)
+    if args.workload == "10Mx768" and args.k == 10:
+        w3 = dict(n=12_500_000, d=384, dtype="bf16")
+        st3 = fill_store(pkg, torch, w3, rank * w3["n"], (rank + 1) * w3["n"], local)
+        s3 = pkg.ShardedSearcher(st3, rank * w3["n"], exchange=args.exchange)
+        case(s3, st3, w3["n"] * world, w3, "12.5Mx384 bf16 per GPU (configs[4] at 8)", 4096, 100, 5)
+        s3.check()
+        st3.close()
+    return out if rank == 0 else []
 
 
 def latency_case(pkg, torch, device):
@@ -715,10 +749,21 @@ def ingest_case(pkg, torch, pk, pk_src, device):
     peak = float(pk["hbm_gbs"])
     return {"workload": f"ingest: pool+normalise+fp16 pack, {chunks} chunks x (256 x 384) fp16, u8 mask", "value": chunks / (ms / 1e3),
             "unit": "chunks/s", "ms_total": ms, "cpu_baseline": cpu,
-            "roofline": {"bound": "hbm", "achieved": bytes_full / ms / 1e6, "achieved_valid_tokens_only": bytes_valid / ms / 1e6,
-                         "peak": peak, "unit": "GB/s", "frac": bytes_full / ms / 1e6 / peak,
-                         "frac_valid_tokens_only": bytes_valid / ms / 1e6 / peak, "traffic": None, "peak_source": pk_src,
-                         "note": "197 636 B/chunk algorithmic (SURVEY 8d); the kernel skips masked tokens, so it can read above 1.0 of that figure"}}
+            "roofline": ingest_roofline(bytes_valid, bytes_full, ms, n_slabs, peak, pk_src)}
+
+
+def ingest_roofline(bytes_valid, bytes_full, ms, launches, peak, pk_src):
+    """The kernel never fetches masked tokens (lengths U{16..256}: about 53 % of a chunk is valid), so the bytes it
+    moves — and the roofline it is held to — are the valid tokens' (+ mask, output row, norm); the 197 636 B/chunk
+    figure of SURVEY 8d is kept beside it as frac_algorithmic."""
+    roof = {"bound": "hbm", "achieved": bytes_valid / ms / 1e6, "peak": peak, "unit": "GB/s",
+            "frac": bytes_valid / ms / 1e6 / peak, "achieved_algorithmic": bytes_full / ms / 1e6,
+            "frac_algorithmic": bytes_full / ms / 1e6 / peak, "traffic": None, "peak_source": pk_src,
+            "kernel": "pool_norm_pack_kernel", "launches_timed": launches, "kernel_ms": ms / launches,
+            "note": "achieved/frac: bytes of the valid tokens + mask + packed row + norm, per launch of 16384 chunks; "
+                    "frac_algorithmic: 197 636 B/chunk (SURVEY 8d) although masked tokens are never read"}
+    attach_traffic(roof, "ingest_pool_fp16_16384x256x384")
+    return roof
 
 
 def main():
