@@ -108,7 +108,8 @@ int CtxLease::acquire() {
   for (;;) {
     if (!s->free_ctx.empty()) { c = s->free_ctx.back(); s->free_ctx.pop_back(); return RAGB_OK; }
     if ((int)s->all_ctx.size() < kMaxCtx) {
-      SearchCtx* n = ctx_new();
+      DeviceGuard g(s->device);  // the stream, events and buffers of a context belong to the store's device
+      SearchCtx* n = g.ok ? ctx_new() : nullptr;
       if (!n) return fail(RAGB_ENOMEM, "cannot create a search context on device %d", s->device);
       s->all_ctx.push_back(n);
       c = n;
