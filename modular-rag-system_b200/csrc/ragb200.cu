@@ -490,6 +490,10 @@ extern "C" int ragb_store_get_rows(ragb_store* s, int64_t row0, int64_t n, void*
 // ---------------------------------------------------------------------------
 // search: K3 scan (+K5 merge) dispatch
 // ---------------------------------------------------------------------------
+static int env_int(const char* name, int dflt) {
+  const char* v = getenv(name);
+  return (v && *v) ? atoi(v) : dflt;
+}
 static bool cpl_ok(int c) { return c == 1 || c == 2 || c == 3 || c == 4 || c == 6 || c == 8; }
 
 static int scan_launch(ragb_store* s, const ScanParams& p, int64_t nq, cudaStream_t st, int* n_lists) {
@@ -504,7 +508,12 @@ static int scan_launch(ragb_store* s, const ScanParams& p, int64_t nq, cudaStrea
   if (generic) kern = k_scan_generic(s->dtype, &R);
   if (!kern) return fail(RAGB_EINVAL, "bad dtype %d", s->dtype);
   const int64_t units = (p.row_end - p.row_begin + R - 1) / R;
-  int P = (int)std::min<int64_t>((units + kScanWarps - 1) / kScanWarps, 2 * (int64_t)s->n_sm);
+  // Small windows (BASELINE configs[0]: 10k rows, 15 MB, L2 resident) are latency-bound, and most of that latency is the
+  // per-CTA list reduction and the last CTA folding one list per CTA: give every warp a few units before adding CTAs
+  // (RAGB_SCAN_UPW, default 4: 10k x 384 fp32 runs on 79 CTAs instead of 296).  Large windows hit the 2-CTAs-per-SM cap
+  // either way.
+  static const int upw = std::max(1, env_int("RAGB_SCAN_UPW", 4));
+  int P = (int)std::min<int64_t>((units + kScanWarps * upw - 1) / (kScanWarps * upw), 2 * (int64_t)s->n_sm);
   if (P < 1) P = 1;
   *n_lists = P;
   if (!p.out) return RAGB_OK;  // sizing pass
@@ -563,10 +572,6 @@ static int make_map(GemmShared* g, CUtensorMap* map, int dtype, const void* base
   return RAGB_OK;
 }
 
-static int env_int(const char* name, int dflt) {
-  const char* v = getenv(name);
-  return (v && *v) ? atoi(v) : dflt;
-}
 static bool pair_enabled() { return env_int("RAGB_PAIR", 1) && !env_int("RAGB_GEMM_SS", 0) && !env_int("RAGB_TS", 0); }
 
 static bool gemm_eligible(const ragb_store* s, int64_t nq, int k, int flags, int64_t n_rows) {
@@ -1337,14 +1342,20 @@ extern "C" int ragb_search(ragb_store* s, const float* q, int64_t nq, int k, int
   char* h = (char*)c->pin;
   RB_TRY(store_prepare_stream(s, c, c->stream, false));
   memcpy(h, q, qb);
-  CU_TRY(cudaMemcpyAsync(d, h, qb, cudaMemcpyHostToDevice, c->stream));
+  // Small calls are all latency (BASELINE configs[0]: one query against 10k rows): pinned host memory is mapped into the
+  // device's address space, so the kernels can read the queries from it and write the k winners straight into it —
+  // no copy engine round trips on either side of the launch.  RAGB_ZERO_COPY: bit 0 = results, bit 1 = queries.
+  static const int zc = env_int("RAGB_ZERO_COPY", 1);
+  const bool zc_out = (zc & 1) && sb + ib <= 65536;
+  const bool zc_in = (zc & 2) && qb <= 16384;
+  if (!zc_in) CU_TRY(cudaMemcpyAsync(d, h, qb, cudaMemcpyHostToDevice, c->stream));
   if (valid) CU_TRY(cudaMemcpyAsync(d + o_v, valid, vb, cudaMemcpyHostToDevice, c->stream));
   SearchReq r;
-  r.q = (const float*)d; r.nq = nq; r.k = k; r.metric = metric; r.threshold = threshold; r.flags = flags;
+  r.q = (const float*)(zc_in ? h : d); r.nq = nq; r.k = k; r.metric = metric; r.threshold = threshold; r.flags = flags;
   r.rb = row_begin; r.re = row_end; r.valid = valid ? (const uint8_t*)(d + o_v) : valid_dev;
-  r.out_scores = (float*)(d + o_s); r.out_ids = (int64_t*)(d + o_i);
+  r.out_scores = (float*)((zc_out ? h : d) + o_s); r.out_ids = (int64_t*)((zc_out ? h : d) + o_i);
   RB_TRY(search_core(s, c, r, c->stream));
-  CU_TRY(cudaMemcpyAsync(h + o_s, d + o_s, o_v - o_s, cudaMemcpyDeviceToHost, c->stream));
+  if (!zc_out) CU_TRY(cudaMemcpyAsync(h + o_s, d + o_s, o_v - o_s, cudaMemcpyDeviceToHost, c->stream));
   CU_TRY(cudaStreamSynchronize(c->stream));
   memcpy(out_scores, h + o_s, sb);
   memcpy(out_ids, h + o_i, ib);

@@ -190,3 +190,28 @@ def test_resident_query_tile_and_shared_threshold_switches(dim, nq, k, monkeypat
     top = set(int(x) for x in got[0][0][0][:min(k, 41)])
     assert top <= ({123} | set(range(50000, 50040)))
     s.close()
+
+
+@pytest.mark.parametrize("k,dtype", [(64, "fp16"), (100, "bf16"), (20, "fp16")])
+def test_masked_epilogue_large_k_vs_oracle(k, dtype):
+    """The masked epilogue (valid mask, row window ending inside a tile) of the SM-pair kernel for every candidate-buffer
+    variant — shared memory (k <= 32) and global memory (kpad 64 / 128) — against the oracle and the scan."""
+    FORCE_GEMM, FORCE_SCAN, _ = _flags()
+    rng = np.random.default_rng(k)
+    n, dim, nq = 33_333, 192, 260
+    X = rng.standard_normal((n, dim)).astype(np.float32)
+    Q = rng.standard_normal((nq, dim)).astype(np.float32)
+    for i in range(0, nq, 13):
+        Q[i] = X[(i * 211) % 30_000] + 0.3 * rng.standard_normal(dim).astype(np.float32)
+    valid = (rng.random(n) > 0.3).astype(np.uint8)
+    valid[4096:4608] = 0                                  # two whole tiles masked out
+    s = _store(X, dtype)
+    rb, re = 517, 31_991                                  # neither end on a 16-row chunk or a 256-row tile
+    ids, sc = s.search(Q, k, "cosine", valid=valid, row_begin=rb, row_end=re, flags=FORCE_GEMM)
+    vmask = valid.astype(bool) & (np.arange(n) >= rb) & (np.arange(n) < re)
+    _check(ids, sc, X, Q, k, "cosine", -np.inf, False, TOL[dtype], valid=vmask)
+    assert vmask[ids[ids >= 0]].all()
+    a_ids, a_sc = s.search(Q, k, "cosine", valid=valid, row_begin=rb, row_end=re, flags=FORCE_SCAN)
+    same = a_ids == ids
+    assert same.mean() > 0.99 and np.abs(a_sc[same] - sc[same]).max() < 2e-6
+    s.close()

@@ -173,3 +173,68 @@ def test_launch_counter_moves():
     s = _store(np.eye(16, dtype=np.float32), "fp16")
     s.search(np.ones(16, np.float32), 2)
     assert launch_count() >= before + 2  # normalise+pack, scan with the fused final merge
+
+
+def test_clear_resets_row_metadata():
+    """ragb_store_clear: rows added after a clear are undescribed again — live, searchable, source 0 — whatever the
+    rows that used to sit there were marked as."""
+    from modular_rag_system_b200 import DeviceStore
+    rng = np.random.default_rng(6)
+    X = rng.standard_normal((500, 32)).astype(np.float32)
+    s = DeviceStore(32, "fp16", 600)
+    s.add(X)
+    s.set_meta(0, np.zeros(500, np.uint8), np.full(500, 9, np.uint16))     # everything retired, source 9
+    s.set_timestamps(0, np.arange(500, 0, -1).astype(np.float64))          # and out of order
+    assert s.build_filter(None, None) == 0
+    s.clear()
+    s.add(X[:300])
+    assert s.build_filter(None, None) == 300
+    ids, _ = s.search(X[7], 1, "cosine", valid="filter")
+    assert ids[0][0] == 7
+    allowed = np.zeros(10, np.uint8); allowed[9] = 1
+    assert s.build_filter(allowed, None) == 0                               # the old source codes are gone
+    X2 = X.copy(); X2[299] = X2[5]
+    s.clear(); s.add(X2[:300])
+    assert s.search(X2[5], 2, "cosine")[0][0].tolist() == [299, 5]          # row order again, not the old timestamps
+    s.close()
+
+
+def test_concurrent_readers_overlap():
+    """Searches of different threads lease their own stream + workspace (csrc/store.h: SearchCtx) instead of queueing on
+    one: 8 reader threads on BASELINE configs[0]'s shape (10k x 384 fp32, cosine top-5, one query per call — what the
+    reference's GUI does, rag_query_interface.py:740-744) answer the same queries correctly, and more of them per
+    second than one thread."""
+    import threading
+    import time
+    from modular_rag_system_b200 import DeviceStore
+    rng = np.random.default_rng(2)
+    n, d = 10_000, 384
+    X = rng.standard_normal((n, d)).astype(np.float32)
+    s = DeviceStore(d, "fp32", n)
+    s.add(X)
+    Q = X[rng.integers(0, n, 64)] + 0.1 * rng.standard_normal((64, d)).astype(np.float32)
+    want = [s.search(q, 5, "cosine", clamp01=True) for q in Q]
+
+    def run(n_threads, seconds=1.0):
+        stop, counts, bad = time.perf_counter() + seconds, [0] * n_threads, []
+
+        def reader(t):
+            i = t
+            while time.perf_counter() < stop:
+                ids, sc = s.search(Q[i % 64], 5, "cosine", clamp01=True)
+                if not (np.array_equal(ids, want[i % 64][0]) and np.array_equal(sc, want[i % 64][1])):
+                    bad.append(i)
+                counts[t] += 1
+                i += n_threads
+        th = [threading.Thread(target=reader, args=(t,)) for t in range(n_threads)]
+        t0 = time.perf_counter()
+        [t.start() for t in th]
+        [t.join() for t in th]
+        assert not bad
+        return sum(counts) / (time.perf_counter() - t0)
+
+    run(2, 0.2)
+    one, eight = run(1), run(8)
+    print(f"queries/s: 1 thread {one:.0f}, 8 threads {eight:.0f} ({eight / one:.2f}x)")
+    assert eight > 1.5 * one, (one, eight)
+    s.close()
