@@ -256,7 +256,21 @@ struct EpiCtx {
   int cnt;
   int sorted;           // keys at the front of the buffer still sorted from the last prune
   float user_fast, fthr;
+  // kEpi8 (two epilogue warps per TMEM lane quarter, each reading half of the accumulator's columns): the two threads
+  // of a query share its buffer, so the count / sorted prefix / threshold live in shared memory, [128] each
+  int* cnt_s;           // this query's entry
+  int* sorted_s;
+  float* thr_s;
 };
+// append a candidate key to the query's buffer
+template <bool kEpi8>
+__device__ __forceinline__ void epi_push(EpiCtx& e, uint64_t key) {
+  if constexpr (kEpi8) e.my[atomicAdd(e.cnt_s, 1)] = key;   // rare: about k*ln(chunks/k) times per query and CTA
+  else e.my[e.cnt++] = key;
+}
+__device__ __forceinline__ void named_bar_sync(int id, int threads) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory");
+}
 // max of 16 consecutive columns: five 3-input maxima, then 6 -> 2 -> 1
 __device__ __forceinline__ float max16(const uint32_t* r) {
   float t[5];
@@ -266,7 +280,7 @@ __device__ __forceinline__ float max16(const uint32_t* r) {
   return fmaxf(fmax3(t[0], t[1], t[2]), fmax3(t[3], t[4], __uint_as_float(r[15])));
 }
 // one tcgen05.ld of 32 columns = two chunks of 16 rows (kRows == 16) or one chunk of 32
-template <bool kMasked, int kRows>
+template <bool kMasked, int kRows, bool kEpi8 = false>
 __device__ __forceinline__ void epi_chunk(EpiCtx& e, uint32_t (&r)[32], int64_t row_c, const TsParams& p, int lane) {
   bool any_a = true, any_b = true;
   if (kMasked) {
@@ -284,11 +298,11 @@ __device__ __forceinline__ void epi_chunk(EpiCtx& e, uint32_t (&r)[32], int64_t 
   }
   const float ma = max16(&r[0]), mb = max16(&r[16]);
   if constexpr (kRows == 16) {
-    if (ma >= e.fthr && any_a) e.my[e.cnt++] = make_key(finish_score(ma, 1.0f, p.flags), (uint32_t)row_c);
-    if (mb >= e.fthr && any_b) e.my[e.cnt++] = make_key(finish_score(mb, 1.0f, p.flags), (uint32_t)row_c + 16);
+    if (ma >= e.fthr && any_a) epi_push<kEpi8>(e, make_key(finish_score(ma, 1.0f, p.flags), (uint32_t)row_c));
+    if (mb >= e.fthr && any_b) epi_push<kEpi8>(e, make_key(finish_score(mb, 1.0f, p.flags), (uint32_t)row_c + 16));
   } else {
     const float mx = fmaxf(ma, mb);
-    if (mx >= e.fthr && (any_a || any_b)) e.my[e.cnt++] = make_key(finish_score(mx, 1.0f, p.flags), (uint32_t)row_c);
+    if (mx >= e.fthr && (any_a || any_b)) epi_push<kEpi8>(e, make_key(finish_score(mx, 1.0f, p.flags), (uint32_t)row_c));
   }
 }
 // once per tile (a query gains at most kPairN / rows-per-chunk = 16 or 8 chunks per tile): prune the buffers that could overflow next tile
@@ -315,13 +329,47 @@ __device__ __forceinline__ void epi_prune(EpiCtx& e, const TsParams& p, int lane
     __syncwarp();
   }
 }
+// kEpi8: the two warps of a lane quarter meet (named barrier: every append of this tile is in the buffers), share the
+// prunes — warp half h takes the queries of its parity — and meet again before the next tile picks up the thresholds
+template <int E, bool Q>
+__device__ __forceinline__ void epi_prune8(EpiCtx& e, const TsParams& p, int lane, int quarter, int half) {
+  constexpr int kCap = CandCfg<E, Q>::cap, kStride = CandCfg<E, Q>::stride;
+  named_bar_sync(1 + quarter, 64);
+  const int my_cnt = *e.cnt_s;
+  unsigned need = __ballot_sync(0xffffffffu, my_cnt > kCap - kPairN / ChunkCfg<E>::rows) & (half ? 0xAAAAAAAAu : 0x55555555u);
+  while (need) {
+    const int j = __ffs(need) - 1;
+    need &= need - 1;
+    const int n = __shfl_sync(0xffffffffu, my_cnt, j);
+    const int sorted = p.full_sort ? 0 : __shfl_sync(0xffffffffu, *e.sorted_s, j);
+    __syncwarp();
+    int keep;
+    const uint64_t kth = warp_prune<E>(e.warp_cand + (size_t)j * kStride, n, p.k, lane, &keep, sorted);
+    if (lane == j) {
+      *e.cnt_s = keep;
+      *e.sorted_s = keep;
+      if (n >= p.k) {
+        const float t = fmaxf(*e.thr_s, fmaxf(e.user_fast, fast_bound(key_score(kth), p.flags)));
+        *e.thr_s = t;
+        if (e.gthr) atomicMax(e.gthr, order_bits(t));
+      }
+    }
+    __syncwarp();
+  }
+  named_bar_sync(1 + quarter, 64);
+  e.fthr = fmaxf(e.fthr, *e.thr_s);
+}
+
 // sort every query's survivors and write kpad keys
 template <int E, bool Q>
-__device__ __forceinline__ void epi_flush(EpiCtx& e, int64_t qrow0, int split, const TsParams& p, int lane) {
+__device__ __forceinline__ void epi_flush(EpiCtx& e, int64_t qrow0, int split, const TsParams& p, int lane, int j0 = 0,
+                                          int jstep = 1, bool shared_state = false) {
   constexpr int kStride = CandCfg<E, Q>::stride;
   __syncwarp();
-  for (int j = 0; j < 32; ++j) {
-    const int n = __shfl_sync(0xffffffffu, e.cnt, j);
+  const int my_cnt = shared_state ? *e.cnt_s : e.cnt;
+  const int my_sorted = shared_state ? *e.sorted_s : e.sorted;
+  for (int j = j0; j < 32; j += jstep) {
+    const int n = __shfl_sync(0xffffffffu, my_cnt, j);
     uint64_t* base = e.warp_cand + (size_t)j * kStride;
     uint64_t* out = p.out + ((size_t)(qrow0 + j) * p.n_splits + split) * p.kpad;
     const int keep = n < p.k ? n : p.k;
@@ -329,7 +377,7 @@ __device__ __forceinline__ void epi_flush(EpiCtx& e, int64_t qrow0, int split, c
       const uint64_t v = warp_top32_of_64(base, n, lane);
       if (lane < p.kpad) out[lane] = lane < keep ? v : 0ull;
     } else {
-      const int sorted = p.full_sort ? 0 : __shfl_sync(0xffffffffu, e.sorted, j);
+      const int sorted = p.full_sort ? 0 : __shfl_sync(0xffffffffu, my_sorted, j);
       if (sorted == 16 * E && p.k == 16 * E) {  // as in warp_prune: the lower half is in order, keep == k == 16*E
         uint64_t lo[E / 2];
         warp_best_half<E>(base, n, lane, lo);
@@ -347,8 +395,14 @@ __device__ __forceinline__ void epi_flush(EpiCtx& e, int64_t qrow0, int split, c
   }
 }
 
-template <int E, int kPairStages, bool kQRes = false>
-__global__ void __launch_bounds__(kGemmThreads, 1)
+// kEpi8: 8 epilogue warps (320 threads).  A warp may only touch the TMEM lanes of its quarter (warp % 4), so warps
+// 2-5 and 6-9 pair up per quarter and split the 256 accumulator columns of a tile between them.  Why: one epilogue warp
+// per scheduler issues a dependent tcgen05.ld -> wait -> max tree -> compare chain (an instruction every ~12 cycles,
+// profiles/r1d_pair_top100_waits.txt); at dim <= 384 a tile's MMA takes 3 072 cycles, the epilogue 2 500 - 3 000, and
+// any prune lands on the critical path (tensor pipe 74 % active at 1M x 384).  Two warps per scheduler overlap those
+// chains, which leaves the TMEM read rate (64 B/cycle: 2 048 cycles per tile) as the epilogue's floor.
+template <int E, int kPairStages, bool kQRes = false, bool kEpi8 = false>
+__global__ void __launch_bounds__(kEpi8 ? kPairThreads8 : kGemmThreads, 1)
 gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_x,
                       const TsParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -367,6 +421,9 @@ gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_co
   uint64_t* tempty_bar = tfull_bar + 2;          // leader's copy is the one in use
   uint64_t* q_bar = tempty_bar + 2;              // kQRes: the query tiles of both CTAs have landed (leader's copy)
   uint32_t* tmem_base_smem = reinterpret_cast<uint32_t*>(q_bar + 1);
+  int* qs_cnt = reinterpret_cast<int*>(tmem_base_smem + 4);  // kEpi8: per-query count | sorted prefix | threshold
+  int* qs_sorted = qs_cnt + kGemmM;
+  float* qs_thr = reinterpret_cast<float*>(qs_sorted + kGemmM);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int rank = blockIdx.x & 1;               // cluster dims (2,1,1): rank == %cluster_ctarank
@@ -378,7 +435,7 @@ gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_co
 
   if (threadIdx.x == 0) {
     for (int i = 0; i < kPairStages; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
-    for (int i = 0; i < 2; ++i) { mbar_init(&tfull_bar[i], 1); mbar_init(&tempty_bar[i], 8); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&tfull_bar[i], 1); mbar_init(&tempty_bar[i], kEpi8 ? 16 : 8); }
     mbar_init(q_bar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -469,8 +526,9 @@ gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_co
       }
     }
   } else {
-    // ===== epilogue (both CTAs): thread == query =====
+    // ===== epilogue (both CTAs): thread == query (kEpi8: two threads per query, half of the columns each) =====
     const int quarter = warp & 3;
+    const int half = kEpi8 ? ((warp - 2) >> 2) : 0;
     const int tid = quarter * 32 + lane;
     const uint32_t lane_base = tmem_base + ((uint32_t)(quarter * 32) << 16);
     EpiCtx e;
@@ -483,6 +541,20 @@ gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_co
     // the 16-bit-query scores only SELECT: the user threshold is applied with slack here, exactly by the re-score
     e.user_fast = ((int64_t)qt * kGemmM + tid < p.nq) ? fast_bound(p.threshold - p.sel_slack, p.flags) : INFINITY;
     e.fthr = e.user_fast;
+    if constexpr (E == 2) {
+      // the shared-memory variants are full to the last kilobyte: the per-query words sit in the padding slot each
+      // buffer carries for bank spread (slot `cap` of `stride` = cap + 1); no sorted prefix is kept for E == 2
+      int* pad = reinterpret_cast<int*>(e.my + Cand::cap);
+      e.cnt_s = pad; e.sorted_s = pad; e.thr_s = reinterpret_cast<float*>(pad + 1);
+    } else {
+      e.cnt_s = qs_cnt + tid; e.sorted_s = qs_sorted + tid; e.thr_s = qs_thr + tid;
+    }
+    if constexpr (kEpi8) {
+      if (half == 0) { *e.cnt_s = 0; *e.sorted_s = 0; *e.thr_s = e.user_fast; }
+      named_bar_sync(1 + quarter, 64);
+    }
+    constexpr int kBlocks = kPairN / 32;                     // tcgen05.ld blocks of 32 columns per tile
+    const int c_lo = kEpi8 ? half * (kBlocks / 2) : 0, c_hi = kEpi8 ? c_lo + kBlocks / 2 : kBlocks;
     uint32_t acc = 0, aph = 0;
     for (int64_t t = t0; t < t1; ++t) {
       const int64_t row0 = p.row_begin + t * kPairN;
@@ -493,35 +565,38 @@ gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_co
       const uint32_t taddr = lane_base + acc * (uint32_t)kPairN;
       // two register sets: the TMEM load of the next 32 columns is in flight while this one is examined
       uint32_t ra[32], rb[32];
-      tc_ld32(taddr, ra);
+      tc_ld32(taddr + c_lo * 32, ra);
       if (p.valid == nullptr && row0 + kPairN <= p.row_end) {
 #pragma unroll 1
-        for (int c = 0; c < kPairN / 32; c += 2) {
+        for (int c = c_lo; c < c_hi; c += 2) {
           tc_wait_ld_dep(ra);
           tc_ld32(taddr + (c + 1) * 32, rb);
-          epi_chunk<false, ChunkCfg<E>::rows>(e, ra, row0 + c * 32, p, lane);
+          epi_chunk<false, ChunkCfg<E>::rows, kEpi8>(e, ra, row0 + c * 32, p, lane);
           tc_wait_ld_dep(rb);
-          if (c + 2 < kPairN / 32) tc_ld32(taddr + (c + 2) * 32, ra);
-          epi_chunk<false, ChunkCfg<E>::rows>(e, rb, row0 + (c + 1) * 32, p, lane);
+          if (c + 2 < c_hi) tc_ld32(taddr + (c + 2) * 32, ra);
+          epi_chunk<false, ChunkCfg<E>::rows, kEpi8>(e, rb, row0 + (c + 1) * 32, p, lane);
         }
       } else {  // valid mask given, or the tile reaches past row_end
 #pragma unroll 1
-        for (int c = 0; c < kPairN / 32; c += 2) {
+        for (int c = c_lo; c < c_hi; c += 2) {
           tc_wait_ld_dep(ra);
           tc_ld32(taddr + (c + 1) * 32, rb);
-          epi_chunk<true, ChunkCfg<E>::rows>(e, ra, row0 + c * 32, p, lane);
+          epi_chunk<true, ChunkCfg<E>::rows, kEpi8>(e, ra, row0 + c * 32, p, lane);
           tc_wait_ld_dep(rb);
-          if (c + 2 < kPairN / 32) tc_ld32(taddr + (c + 2) * 32, ra);
-          epi_chunk<true, ChunkCfg<E>::rows>(e, rb, row0 + (c + 1) * 32, p, lane);
+          if (c + 2 < c_hi) tc_ld32(taddr + (c + 2) * 32, ra);
+          epi_chunk<true, ChunkCfg<E>::rows, kEpi8>(e, rb, row0 + (c + 1) * 32, p, lane);
         }
       }
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive_cta(&tempty_bar[acc], 0);
       if ((acc ^= 1) == 0) aph ^= 1;
-      epi_prune<E, kQRes>(e, p, lane);  // after the accumulator is handed back: off the MMA's critical path
+      // after the accumulator is handed back: off the MMA's critical path
+      if constexpr (kEpi8) epi_prune8<E, kQRes>(e, p, lane, quarter, half);
+      else epi_prune<E, kQRes>(e, p, lane);
     }
-    epi_flush<E, kQRes>(e, (int64_t)qt * kGemmM + quarter * 32, split, p, lane);
+    if constexpr (kEpi8) epi_flush<E, kQRes>(e, (int64_t)qt * kGemmM + quarter * 32, split, p, lane, half, 2, true);
+    else epi_flush<E, kQRes>(e, (int64_t)qt * kGemmM + quarter * 32, split, p, lane);
   }
 
   tc_fence_before();

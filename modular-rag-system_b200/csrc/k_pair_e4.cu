@@ -2,7 +2,9 @@
 #include "gemm_pair.cuh"
 #include "kernels.h"
 namespace ragb {
-const void* k_pair_e4(bool qres) {
-  return qres ? (const void*)gemm_topk_pair_kernel<4, kPairStagesLargeQ, true> : (const void*)gemm_topk_pair_kernel<4, kPairStagesLarge, false>;
+const void* k_pair_e4(bool qres, bool epi8) {
+  if (epi8)
+    return qres ? (const void*)gemm_topk_pair_kernel<4, kPairStagesLargeQ, true, true> : (const void*)gemm_topk_pair_kernel<4, kPairStagesLarge, false, true>;
+  return qres ? (const void*)gemm_topk_pair_kernel<4, kPairStagesLargeQ, true, false> : (const void*)gemm_topk_pair_kernel<4, kPairStagesLarge, false, false>;
 }
 }  // namespace ragb

@@ -8,11 +8,13 @@
 
 namespace ragb {
 
-// gemm_pair.cuh: gemm_topk_pair_kernel<E, stages, qres>(CUtensorMap map_q, CUtensorMap map_x, TsParams)
-const void* k_pair_e2(bool qres);
-const void* k_pair_e4(bool qres);
-const void* k_pair_e8(bool qres);
-inline const void* k_pair(int E, bool qres) { return E == 2 ? k_pair_e2(qres) : E == 4 ? k_pair_e4(qres) : k_pair_e8(qres); }
+// gemm_pair.cuh: gemm_topk_pair_kernel<E, stages, qres, epi8>(CUtensorMap map_q, CUtensorMap map_x, TsParams)
+const void* k_pair_e2(bool qres, bool epi8);
+const void* k_pair_e4(bool qres, bool epi8);
+const void* k_pair_e8(bool qres, bool epi8);
+inline const void* k_pair(int E, bool qres, bool epi8) {
+  return E == 2 ? k_pair_e2(qres, epi8) : E == 4 ? k_pair_e4(qres, epi8) : k_pair_e8(qres, epi8);
+}
 // gemm_ts.cuh / gemm_topk.cuh (single-CTA fallbacks), query conversion, fp32 re-score
 const void* k_ts(bool ts);                  // gemm_topk_ts_kernel<ts>(map_q, map_x, TsParams)
 const void* k_gemm_topk();                  // gemm_topk_kernel(map_q, map_x, GemmParams)

@@ -78,6 +78,7 @@ struct TsParams {
 // ---- gemm_pair.cuh ---------------------------------------------------------------------------------------
 constexpr int kPairStagesSmall = 5;              // ring depth next to the shared-memory candidate buffers (kpad <= 32)
 constexpr int kPairStagesLarge = 6;              // kpad 64 / 128: candidates live in global memory
+constexpr int kPairThreads8 = 320;                // producer + MMA + 8 epilogue warps (gemm_pair.cuh: kEpi8)
 constexpr int kPairN = 256;                       // corpus rows per accumulator tile (both halves)
 constexpr int kPairStageBytes = 2 * kStageBytesA; // 16 KB queries + 16 KB half corpus tile
 constexpr int kPairSyncTiles = 8;                 // default tiles between two meetings of the pairs that share a row split

@@ -659,12 +659,18 @@ static int gemm_pair_launch(ragb_store* s, SearchCtx* c, const SearchReq& r, cud
   const int n_stages = qres ? (E == 2 ? kPairStagesSmallQ : kPairStagesLargeQ) : (E == 2 ? kPairStagesSmall : kPairStagesLarge);
   const size_t cand_stride = E == 2 ? (qres ? kPairCapSmallQ : kPairCapSmall) + 1 : 32 * E;
   const size_t smem = 1024 + (qres ? (size_t)n_kb * kStageBytesA + (size_t)n_stages * kStageBytesA : (size_t)n_stages * kPairStageBytes) +
-                      (E == 2 ? (size_t)kGemmM * cand_stride * 8 : 0) + (2 * n_stages + 5) * 8 + 16;
-  const void* kern = k_pair(E, qres);
-  const int ei = (E == 2 ? 0 : E == 4 ? 1 : 2) + (qres ? 3 : 0);
+                      (E == 2 ? (size_t)kGemmM * cand_stride * 8 : 0) + (2 * n_stages + 5) * 8 + 16 +
+                      (E == 2 ? 0 : 16 + 3 * kGemmM * 4);  // kEpi8, global-memory buffers: per-query count | sorted | threshold
+  // 8 epilogue warps (gemm_pair.cuh: kEpi8).  Measured on B200 against 4 (profiles/r2_epi8_ab.txt): 1M x 384 top-10
+  // kernel 0.614 -> 0.545 ms (1 281 -> 1 442 TFLOP/s), top-100 1.351 -> 1.144 ms, 10M x 384 6.29 -> 5.92 ms, 12.5M x 384
+  // bf16 top-100 15.64 -> 15.33 ms per launch; at dim 768, where the tensor pipe was already 97 % busy, 12.32 -> 12.30 ms.
+  // RAGB_PAIR_EPI8=0 brings the 4-warp epilogue back for A/B runs.
+  const bool epi8 = env_int("RAGB_PAIR_EPI8", 1) != 0;
+  const void* kern = k_pair(E, qres, epi8);
+  const int ei = (E == 2 ? 0 : E == 4 ? 1 : 2) + (qres ? 3 : 0) + (epi8 ? 6 : 0);
   cudaLaunchConfig_t cfg = {};
   cudaLaunchAttribute attr[2];
-  cfg.blockDim = dim3(kGemmThreads); cfg.dynamicSmemBytes = smem; cfg.stream = st;
+  cfg.blockDim = dim3(epi8 ? kPairThreads8 : kGemmThreads); cfg.dynamicSmemBytes = smem; cfg.stream = st;
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
   attr[1].id = cudaLaunchAttributeCooperative;  // only counted in numAttrs when the pairs meet (below)
