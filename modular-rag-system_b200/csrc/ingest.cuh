@@ -97,64 +97,85 @@ __global__ void __launch_bounds__(256) norm_pack_kernel(const Tin* __restrict__ 
   if (lane == 0 && norms) norms[row] = nrm;
 }
 
-// K2, rows of at most 256*CPL elements: a warp takes R consecutive rows, fetches each ONCE (streaming 128-bit loads,
-// all R*CPL of a lane issued before the first is used) and keeps them in registers between the sum of squares and
-// the divide.  R is chosen by the host (1 today: more rows per warp cost more in occupancy than the extra bytes in
-// flight return, see norm_pack_launch).  Same summation order per row as the generic kernel
-// above (lane-serial over its chunks, then the shuffle tree), so both produce the same bits.
-template <typename Tin, typename Tout, int CPL, int R>
-__global__ void __launch_bounds__(256) norm_pack_reg_kernel(const Tin* __restrict__ in, int64_t n, int dim,
+// 8 floats -> 8 packed elements with the paired converts (cvt.rn.f16x2.f32 / cvt.rn.bf16x2.f32): half the convert
+// instructions of the element-wise path
+__device__ __forceinline__ void store8_packed(__half* row, int c, const float* f) {
+  union { uint4 v; __half2 h[4]; } u;
+#pragma unroll
+  for (int e = 0; e < 4; ++e) u.h[e] = __floats2half2_rn(f[2 * e], f[2 * e + 1]);
+  *reinterpret_cast<uint4*>(row + c * 8) = u.v;
+}
+__device__ __forceinline__ void store8_packed(__nv_bfloat16* row, int c, const float* f) {
+  union { uint4 v; __nv_bfloat162 h[4]; } u;
+#pragma unroll
+  for (int e = 0; e < 4; ++e) u.h[e] = __floats2bfloat162_rn(f[2 * e], f[2 * e + 1]);
+  *reinterpret_cast<uint4*>(row + c * 8) = u.v;
+}
+__device__ __forceinline__ void store8_packed(float* row, int c, const float* f) { store8(row, c, f); }
+
+// K2, rows of at most 32*CPL chunks of 8 elements: G lanes own a row (32/G rows per warp), each lane fetches its CPL
+// chunks ONCE (streaming 128-bit loads, all issued before the first is used) and keeps them in registers between the
+// sum of squares and the scaling.  G is picked by the host so that G*CPL wastes as few lane slots as possible: a
+// 384-element row is 48 chunks = 16 lanes x 3, two rows per warp with every lane busy — against 32 lanes x 2 with a
+// quarter of the load slots idle, which together with an IEEE divide per element kept the fp16 -> fp16 case at 0.52 of
+// the HBM peak (instruction-bound: half the bytes of the fp32-input case for the same instruction count).  16-bit
+// outputs are scaled by the reciprocal of the norm (one divide per row; the product differs from the quotient by at
+// most one fp32 ulp, which survives the rounding to 16 bits about once in 2^13 elements); fp32 outputs keep the
+// divide, so that they stay the quotient numpy computes (ollama_rag_system.py:380).
+template <typename Tin, typename Tout, int G, int CPL>
+__global__ void __launch_bounds__(256) norm_pack_sub_kernel(const Tin* __restrict__ in, int64_t n, int dim,
                                                             int64_t ld_in, Tout* __restrict__ out,
                                                             int64_t ld_out, float* __restrict__ norms,
                                                             bool vec_ok) {
-  const int lane = threadIdx.x & 31;
-  const int64_t row0 = ((int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) * R;
-  if (row0 >= n) return;
+  constexpr int RPW = 32 / G;
+  const int lane = threadIdx.x & 31, gl = lane % G, gr = lane / G;
+  const int64_t row = ((int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) * RPW + gr;
+  const bool live = row < n;
   const int chunks_in = (dim + 7) / 8, chunks_out = (int)(ld_out / 8);
-  float f[R][CPL][8];
+  const Tin* src = in + (live ? row : 0) * ld_in;
+  float f[CPL][8];
 #pragma unroll
-  for (int r = 0; r < R; ++r) {
-    const Tin* src = in + (row0 + r) * ld_in;
+  for (int j = 0; j < CPL; ++j) {
+    const int c = gl + G * j;
+    if (live && c < chunks_in) load8_stream(src, c, dim, vec_ok, f[j]);
+    else {
 #pragma unroll
-    for (int j = 0; j < CPL; ++j) {
-      const int c = lane + 32 * j;
-      if (c < chunks_in && row0 + r < n) load8_stream(src, c, dim, vec_ok, f[r][j]);
-      else {
-#pragma unroll
-        for (int e = 0; e < 8; ++e) f[r][j][e] = 0.f;
-      }
+      for (int e = 0; e < 8; ++e) f[j][e] = 0.f;
     }
   }
-  float ss[R];
+  float ss = 0.f;
 #pragma unroll
-  for (int r = 0; r < R; ++r) {
-    ss[r] = 0.f;
+  for (int j = 0; j < CPL; ++j)
 #pragma unroll
-    for (int j = 0; j < CPL; ++j) {
-      if (lane + 32 * j < chunks_in) {
+    for (int e = 0; e < 8; ++e) ss = fmaf(f[j][e], f[j][e], ss);
 #pragma unroll
-        for (int e = 0; e < 8; ++e) ss[r] = fmaf(f[r][j][e], f[r][j][e], ss[r]);
-      }
-    }
-  }
-#pragma unroll
-  for (int r = 0; r < R; ++r) ss[r] = warp_sum(ss[r]);
-#pragma unroll
-  for (int r = 0; r < R; ++r) {
-    if (row0 + r >= n) break;
-    const float nrm = sqrtf(ss[r]);
-    Tout* dst = out + (row0 + r) * ld_out;
+  for (int o = G / 2; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
+  const float nrm = sqrtf(ss);
+  if (!live) return;
+  Tout* dst = out + row * ld_out;
+  if constexpr (sizeof(Tout) == 2) {
+    const float inv = nrm > 0.f ? __fdiv_rn(1.0f, nrm) : 0.f;
 #pragma unroll
     for (int j = 0; j < CPL; ++j) {
-      const int c = lane + 32 * j;
+      const int c = gl + G * j;
       if (c < chunks_out) {
 #pragma unroll
-        for (int e = 0; e < 8; ++e) f[r][j][e] = nrm > 0.f ? __fdiv_rn(f[r][j][e], nrm) : 0.f;
-        store8(dst, c, f[r][j]);
+        for (int e = 0; e < 8; ++e) f[j][e] *= inv;
+        store8_packed(dst, c, f[j]);
       }
     }
-    if (lane == 0 && norms) norms[row0 + r] = nrm;
+  } else {
+#pragma unroll
+    for (int j = 0; j < CPL; ++j) {
+      const int c = gl + G * j;
+      if (c < chunks_out) {
+#pragma unroll
+        for (int e = 0; e < 8; ++e) f[j][e] = nrm > 0.f ? __fdiv_rn(f[j][e], nrm) : 0.f;
+        store8(dst, c, f[j]);
+      }
+    }
   }
+  if (gl == 0 && norms) norms[row] = nrm;
 }
 
 // ---- K1 -------------------------------------------------------------------

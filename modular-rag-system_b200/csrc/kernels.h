@@ -35,7 +35,7 @@ const void* k_rank_scatter();
 const void* k_scan(int dtype, int G, int cpl, int* rows_per_warp_iter);
 const void* k_scan_generic(int dtype, int* rows_per_warp_iter);
 // ingest.cuh
-const void* k_norm_pack(int tin, int tout, int cpl);   // cpl 1..4: norm_pack_reg_kernel<Tin,Tout,cpl,1>; 0: norm_pack_kernel
+const void* k_norm_pack(int tin, int tout, int G, int cpl);   // norm_pack_sub_kernel<Tin,Tout,G,cpl>; G == 0: norm_pack_kernel (any length)
 const void* k_pool(int tin, int tm, int tout);         // pool_norm_pack_kernel<Tin,Tm,Tout>
 int pool_threads();
 

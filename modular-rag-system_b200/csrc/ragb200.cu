@@ -274,10 +274,22 @@ static int norm_pack_any(const void* in, int in_dtype, int64_t n, int dim, int64
   const bool vec_ok = ((uintptr_t)in % 16 == 0) && ((ld_in * elem_size(in_dtype)) % 16 == 0);
   const int64_t chunks = std::max<int64_t>((dim + 7) / 8, ld_out / 8);
   static const bool generic_only = getenv("RAGB_NORM_PACK_GENERIC") != nullptr;  // A/B runs
-  // one row per warp, fetched once and kept in registers (ingest.cuh); rows longer than 1024 elements: generic kernel
-  const int cpl = (generic_only || chunks > 128) ? 0 : (int)((chunks + 31) / 32);
-  const void* kern = k_norm_pack(in_dtype, out_dtype, cpl);
-  LAUNCH(kern, dim3((unsigned)((n + 7) / 8)), dim3(256), 0, st, in, n, dim, ld_in, out, ld_out, norms, vec_ok);
+  // G lanes per row, CPL chunks per lane, fetched once and kept in registers (ingest.cuh): the (G, CPL) that wastes the
+  // fewest lane slots; rows longer than 1024 elements take the generic two-pass kernel
+  int G = 0, cpl = 0;
+  if (!generic_only && chunks <= 128) {
+    int best_waste = 1 << 30;
+    for (int g = 32; g >= 8; g >>= 1) {
+      const int c = (int)((chunks + g - 1) / g);
+      if (c > (g == 32 ? 4 : 3)) continue;
+      const int waste = g * c - (int)chunks;
+      if (waste < best_waste) { best_waste = waste; G = g; cpl = c; }
+    }
+  }
+  const void* kern = k_norm_pack(in_dtype, out_dtype, G, cpl);
+  if (!kern) return fail(RAGB_EINVAL, "internal: no normalise+pack kernel for G=%d cpl=%d", G, cpl);
+  const int64_t rows_per_cta = 8 * (G ? 32 / G : 1);
+  LAUNCH(kern, dim3((unsigned)((n + rows_per_cta - 1) / rows_per_cta)), dim3(256), 0, st, in, n, dim, ld_in, out, ld_out, norms, vec_ok);
   return RAGB_OK;
 }
 
