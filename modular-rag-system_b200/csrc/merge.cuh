@@ -73,9 +73,12 @@ __device__ __forceinline__ int count_greater_sorted(const uint64_t* list, int le
 }
 
 
+#ifndef RAGB_FINISH_CTAS
+#define RAGB_FINISH_CTAS 3  // co-resident CTAs per SM the register budget is cut for (build-time A/B)
+#endif
 // kRows = rows per chunk: 16 (a half-warp per chunk, two chunks per warp at a time) or 32 (a warp per chunk)
 template <typename T, int kRows>
-__global__ void __launch_bounds__(kMergeThreads, 3) finish_chunks_kernel(const FinishParams p) {
+__global__ void __launch_bounds__(kMergeThreads, RAGB_FINISH_CTAS) finish_chunks_kernel(const FinishParams p) {
   constexpr int kFinishChunkRows = kRows;
   constexpr int kPerWarp = 32 / kRows;            // chunks a warp scores at a time
   constexpr int kLaneMask = kRows - 1;            // lane -> row of its chunk
