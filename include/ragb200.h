@@ -208,6 +208,13 @@ int ragb_search_scatter_dev(ragb_store* s, const float* q, int64_t nq, int k, in
                             void* stream);
 int ragb_gather_merge_dev(int device, const ragb_exchange* x, int64_t nq, int k, float* out_scores,
                           int64_t* out_ids, int* out_status, void* stream);
+/* The two calls above as ONE host entry point (what ragb_search is for a single store): queries from host memory
+ * (identical on every rank), upload, local search + scatter into every rank's gather buffer, wait + merge, results
+ * back into host memory — one stream, one synchronisation, no caller-side copies.  *out_status = 1 if a rank's
+ * candidates did not arrive within the kernel's timeout. */
+int ragb_search_exchange(ragb_store* s, const float* q, int64_t nq, int k, int metric, float threshold, int flags,
+                         uint32_t id_base, const ragb_exchange* x, float* out_scores, int64_t* out_ids,
+                         int* out_status);
 
 /* ---- row-sharded store: ONE process, the rows dealt over several GPUs of one NVSwitch box ------------------------
  * north_star: "the embedding store ... row-sharded across GPUs", behind the same entry points as the one-device store

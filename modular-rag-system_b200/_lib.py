@@ -72,6 +72,7 @@ SIGNATURES = {
     "ragb_merge_keys_dev": (_i, [_i, _vp, _i64, _i, _i, _i64, _i64, _i, _vp, _vp, _vp]),
     "ragb_search_scatter_dev": (_i, [_vp, _vp, _i64, _i, _i, _f, _i, _i64, _i64, _vp, C.c_uint32, C.POINTER(Exchange), _vp]),
     "ragb_gather_merge_dev": (_i, [_i, C.POINTER(Exchange), _i64, _i, _vp, _vp, _vp, _vp]),
+    "ragb_search_exchange": (_i, [_vp, _vp, _i64, _i, _i, _f, _i, C.c_uint32, C.POINTER(Exchange), _vp, _vp, C.POINTER(_i)]),
     # row-sharded store (one process, several GPUs)
     "ragb_mstore_create": (_i, [_i, _i, _i64, C.POINTER(_i), _i, _i64, C.POINTER(_vp)]),
     "ragb_mstore_destroy": (_i, [_vp]),

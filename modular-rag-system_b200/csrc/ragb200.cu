@@ -1322,6 +1322,51 @@ extern "C" int ragb_gather_merge_dev(int device, const ragb_exchange* x, int64_t
                       (cudaStream_t)stream, false, nullptr, x->flags[x->rank], x->world, x->epoch, out_status);
 }
 
+extern "C" int ragb_search_exchange(ragb_store* s, const float* q, int64_t nq, int k, int metric, float threshold,
+                                    int flags, uint32_t id_base, const ragb_exchange* x, float* out_scores,
+                                    int64_t* out_ids, int* out_status) {
+  if (!s) return fail(RAGB_EINVAL, "store is NULL");
+  RB_TRY(check_exchange(x));
+  if (nq <= 0 || !q || !out_scores || !out_ids) return fail(RAGB_EINVAL, "peer exchange needs at least one query and output buffers");
+  std::shared_lock<std::shared_mutex> ls(s->rows_mu);
+  int64_t rb = 0, re = -1;
+  RB_TRY(store_check_args(s, q, nq, k, metric, &rb, &re));
+  ON_DEVICE(s->device);
+  RB_TRY(store_ensure_ranks(s, ls, re));
+  const int kpad = kpad_of(k);
+  const size_t qb = (size_t)nq * s->dim * 4, sb = (size_t)nq * k * 4, ib = (size_t)nq * k * 8;
+  auto al = [](size_t v) { return (v + 255) / 256 * 256; };
+  const size_t o_s = al(qb), o_i = o_s + al(sb), o_st = o_i + al(ib), total = o_st + 256;
+  CtxLease lease(s);
+  RB_TRY(lease.acquire());
+  SearchCtx* c = lease.c;
+  RB_TRY(grow(&c->io, &c->io_bytes, total, false));
+  RB_TRY(grow(&c->pin, &c->pin_bytes, total, true));
+  char* d = (char*)c->io;
+  char* h = (char*)c->pin;
+  RB_TRY(store_prepare_stream(s, c, c->stream, false));
+  memcpy(h, q, qb);
+  *(int*)(h + o_st) = 0;
+  CU_TRY(cudaMemcpyAsync(d, h, qb, cudaMemcpyHostToDevice, c->stream));
+  SearchReq r;
+  r.q = (const float*)d; r.nq = nq; r.k = k; r.metric = metric; r.threshold = threshold; r.flags = flags;
+  r.rb = rb; r.re = re; r.id_base = id_base;
+  r.peer.n = x->world; r.peer.epoch = x->epoch; r.peer.signal = 1; r.peer.done = c->tickets + kScanMaxQ;
+  for (int p = 0; p < x->world; ++p) {
+    r.peer.keys[p] = x->keys[p] + (size_t)x->rank * nq * kpad;
+    r.peer.flag[p] = x->flags[p] + x->rank;
+  }
+  RB_TRY(search_core(s, c, r, c->stream));
+  // the merge writes scores, ids and the timeout status straight into mapped pinned memory: nothing to copy back
+  RB_TRY(merge_launch(x->keys[x->rank], nq, x->world, kpad, kpad, (int64_t)nq * kpad, k, (float*)(h + o_s), (int64_t*)(h + o_i),
+                      nullptr, nullptr, c->stream, false, nullptr, x->flags[x->rank], x->world, x->epoch, (int*)(h + o_st)));
+  CU_TRY(cudaStreamSynchronize(c->stream));
+  memcpy(out_scores, h + o_s, sb);
+  memcpy(out_ids, h + o_i, ib);
+  if (out_status) *out_status = *(int*)(h + o_st);
+  return RAGB_OK;
+}
+
 extern "C" int ragb_search_dev(ragb_store* s, const float* q, int64_t nq, int k, int metric, float threshold, int flags,
                                int64_t row_begin, int64_t row_end, const uint8_t* valid, float* out_scores,
                                int64_t* out_ids, void* stream) {

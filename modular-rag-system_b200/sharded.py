@@ -176,6 +176,15 @@ class ShardedSearcher:
         import torch
         q = np.ascontiguousarray(np.atleast_2d(q), dtype=np.float32)
         dev = torch.device("cuda", self.store.device)
+        if self.world > 1 and self.exchange == "peer":
+            # one C call: upload, local search + scatter, wait + merge, results in mapped pinned memory
+            from .store import kpad_of
+            pb = self._peer_buffers(q.shape[0], kpad_of(k), dev)
+            ids, sc, timed_out = self.store.search_exchange(q, k, pb.next_exchange(), metric, threshold, clamp01,
+                                                            id_base=self.row_base, flags=flags)
+            if timed_out:
+                raise RuntimeError("peer exchange: a rank's candidates did not arrive within the kernel's timeout")
+            return ids, sc
         if getattr(self, "_qpin", None) is None or self._qpin.shape != q.shape:
             self._qpin = torch.empty(q.shape, dtype=torch.float32, pin_memory=True)
             self._qdev = torch.empty(q.shape, dtype=torch.float32, device=dev)

@@ -288,6 +288,22 @@ class DeviceStore:
         check(self._lib.ragb_search_scatter_dev(self._h, q.data_ptr(), q.shape[0], int(k), _METRICS[metric], float(threshold),
                                                 fl, 0, -1, None, int(id_base), C.byref(exchange), _cur_stream(self.device)))
 
+    def search_exchange(self, q: np.ndarray, k: int, exchange, metric: str = "ip", threshold: float = NEG_INF,
+                        clamp01: bool = False, id_base: int = 0, flags: int = 0):
+        """Host entry of the peer-memory exchange (C ABI ragb_search_exchange): numpy queries in, numpy results out,
+        upload + local search + scatter + wait + merge + read-back inside one call on one stream.
+        Returns (ids, scores, timed_out)."""
+        q = np.ascontiguousarray(np.atleast_2d(q), dtype=np.float32)
+        nq = q.shape[0]
+        ids = np.empty((nq, k), dtype=np.int64)
+        scores = np.empty((nq, k), dtype=np.float32)
+        status = C.c_int(0)
+        fl = int(flags) | (CLAMP01 if clamp01 else 0)
+        check(self._lib.ragb_search_exchange(self._h, q.ctypes.data, nq, int(k), _METRICS[metric], float(threshold), fl,
+                                             int(id_base), C.byref(exchange), scores.ctypes.data, ids.ctypes.data,
+                                             C.byref(status)))
+        return ids, scores, bool(status.value)
+
     # -- measurement ------------------------------------------------------------ #
     def profile(self, enable: bool = True) -> None:
         """Bracket the dominant kernel of every later search with CUDA events (bench.py's roofline leg)."""

@@ -101,3 +101,43 @@ def test_peer_exchange_timeout_reports():
     torch.cuda.synchronize()
     assert int(status.item()) == 1
     assert (ids.cpu().numpy()[:, 0] >= 0).all()  # rank 0's candidates are still merged
+
+
+def test_search_exchange_host_entry_two_ranks_in_threads():
+    """ragb_search_exchange — upload + local search + scatter + wait + merge + read-back in ONE host call — with two
+    ranks emulated as two stores on one GPU, each driven by its own thread (a rank's call returns only when the other
+    rank's candidates have arrived)."""
+    import threading
+    import torch
+    from modular_rag_system_b200 import DeviceStore, PeerBuffers, kpad_of, shard_bounds
+    rng = np.random.default_rng(77)
+    n, d, nq, k, world = 8000, 128, 48, 10, 2
+    X = rng.standard_normal((n, d)).astype(np.float32)
+    X[6000] = X[17]
+    full = DeviceStore(d, "fp16", n)
+    full.add(X)
+    kpad = kpad_of(k)
+    blocks = [torch.zeros(PeerBuffers.words(world, nq, kpad), dtype=torch.int64, device="cuda") for _ in range(world)]
+    ptrs = [b.data_ptr() for b in blocks]
+    ranks = []
+    for r, (r0, r1) in enumerate(shard_bounds(n, world)):
+        s = DeviceStore(d, "fp16", r1 - r0)
+        s.add(X[r0:r1])
+        ranks.append((s, r0, PeerBuffers(ptrs, world, r, nq, kpad)))
+    torch.cuda.synchronize()
+    for rnd in range(3):
+        Q = rng.standard_normal((nq, d)).astype(np.float32)
+        Q[0] = X[17]
+        want = full.search(Q, k, "cosine")
+        got = [None] * world
+
+        def run(r):
+            s, r0, pb = ranks[r]
+            got[r] = s.search_exchange(Q, k, pb.next_exchange(), "cosine", id_base=r0)
+        th = [threading.Thread(target=run, args=(r,)) for r in range(world)]
+        [t.start() for t in th]
+        [t.join() for t in th]
+        for ids, sc, timed_out in got:
+            assert not timed_out
+            assert np.array_equal(ids, want[0]) and np.array_equal(sc, want[1])
+            assert ids[0][:2].tolist() == [6000, 17]
