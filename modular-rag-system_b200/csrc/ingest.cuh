@@ -10,6 +10,7 @@
 //     never fetched from HBM.
 #pragma once
 #include "common.cuh"
+#include "params.h"
 
 namespace ragb {
 
@@ -180,6 +181,9 @@ __global__ void __launch_bounds__(256) norm_pack_sub_kernel(const Tin* __restric
 
 // ---- K1 -------------------------------------------------------------------
 template <typename Tm> __device__ __forceinline__ float mask_weight(Tm m) { return (float)m; }
+__device__ __forceinline__ void named_bar_sync_pool(int id, int threads) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory");
+}
 
 // block-wide sum, deterministic; red = 8 floats of shared memory
 __device__ __forceinline__ float block_sum(float v, float* red) {
@@ -332,6 +336,181 @@ __global__ void __launch_bounds__(kPoolThreads, PoolCfg<Tin>::ctas) pool_norm_pa
     store8(dst, c, f);
   }
   if (t == 0 && norms) norms[b] = nrm;
+}
+
+// ---- K1, persistent form -------------------------------------------------------------------------------------------
+// The kernel above gives a CTA one chunk and runs its phases one after the other (mask compaction, loads, block
+// reduction, normalise, store); with ragged lengths U{16..256} the short chunks are mostly fixed cost and nothing is
+// in flight while a CTA is between phases: 0.81 of the HBM peak on the bytes actually read (ncu: DRAM 63 % busy).
+// Here the CTAs are persistent and warp-specialised:
+//   warp 8 (producer)  draws chunks from a global counter (ragged lengths balance themselves), compacts the chunk's
+//                      mask into (token, weight) pairs, and streams the VALID token rows — kPoolRingRows at a time —
+//                      into a ring of shared-memory stages with 1-D TMA (cp.async.bulk, one copy per row issued by
+//                      one lane each, or a single copy when the rows are adjacent), mbarrier per stage;
+//   warps 0-7          wait for a stage, accumulate weight x row into registers straight from shared memory (a
+//                      thread owns 8 consecutive elements; `groups` thread groups take alternate rows), hand the
+//                      stage back, and at a chunk's last stage fold the groups, normalise and store the packed row.
+// The producer runs ahead through the ring across chunk boundaries, so HBM stays busy while the consumers finish a
+// chunk.  Same arithmetic as above (masked mean with max(sum m, 1e-9), v / max(|v|, 1e-12)).
+template <typename Tin, typename Tm, typename Tout>
+__global__ void __launch_bounds__(kPoolRingThreads) pool_ring_kernel(const PoolRingParams p) {
+  extern __shared__ __align__(128) unsigned char psm[];
+  const int C = p.hidden / 8;                       // 8-element columns per row
+  const int groups = kPoolRingConsumers / C;
+  const size_t rb = (size_t)p.hidden * sizeof(Tin);
+  const size_t stage_bytes = (size_t)kPoolRingRows * rb;
+  unsigned char* stages = psm;
+  PoolStageMeta* meta = reinterpret_cast<PoolStageMeta*>(stages + (size_t)p.n_stages * stage_bytes);
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(meta + p.n_stages);
+  uint64_t* empty_bar = full_bar + p.n_stages;
+  const int seq4 = (p.seq + 3) & ~3;
+  int* p_idx = reinterpret_cast<int*>(empty_bar + p.n_stages);
+  float* p_w = reinterpret_cast<float*>(p_idx + seq4);
+  float* accs = p_w + seq4;
+  float* red = accs + (size_t)2 * groups * C * 8;
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+
+  if (t == 0) {
+    for (int i = 0; i < p.n_stages; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], kPoolRingConsumers / 32); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+
+  if (warp == kPoolRingConsumers / 32) {
+    // ===== producer =====
+    const Tin* tok = static_cast<const Tin*>(p.tok);
+    const Tm* mask = static_cast<const Tm*>(p.mask);
+    int s = 0;
+    uint32_t ph = 0;
+    for (;;) {
+      long long b = 0;
+      if (lane == 0) b = (long long)atomicAdd(p.counter, 1ull);
+      b = __shfl_sync(0xffffffffu, b, 0);
+      const bool done = b >= p.batch;
+      int nv = 0;
+      float wsum = 0.f;
+      if (!done) {  // compact the mask: tokens with a non-zero weight, in order
+        for (int s0 = 0; s0 < p.seq; s0 += 32) {
+          const int tk = s0 + lane;
+          const float m = tk < p.seq ? (mask ? (float)mask[b * p.seq + tk] : 1.0f) : 0.f;
+          wsum += m;
+          const unsigned bal = __ballot_sync(0xffffffffu, m != 0.f);
+          if (m != 0.f) {
+            const int pos = nv + __popc(bal & ((1u << lane) - 1u));
+            p_idx[pos] = tk;
+            p_w[pos] = m;
+          }
+          nv += __popc(bal);
+        }
+        wsum = warp_sum(wsum);
+        __syncwarp();
+      }
+      const int n_st = done ? 1 : (nv == 0 ? 1 : (nv + kPoolRingRows - 1) / kPoolRingRows);
+      for (int g = 0; g < n_st; ++g) {
+        mbar_wait(&empty_bar[s], ph ^ 1);
+        const int r0 = g * kPoolRingRows;
+        const int n = done ? -1 : min(kPoolRingRows, nv - r0);
+        PoolStageMeta* mt = &meta[s];
+        if (lane == 0) { mt->n_rows = n; mt->last = (g == n_st - 1) ? 1 : 0; mt->chunk = b; mt->wsum = wsum; }
+        if (n > 0 && lane < n) mt->w[lane] = p_w[r0 + lane];
+        __syncwarp();
+        if (n > 0) {
+          const Tin* base = tok + (size_t)b * p.seq * p.hidden;
+          unsigned char* dst = stages + (size_t)s * stage_bytes;
+          const bool adjacent = p_idx[r0 + n - 1] - p_idx[r0] == n - 1;
+          if (lane == 0) mbar_expect_tx(&full_bar[s], (uint32_t)(n * rb));
+          __syncwarp();
+          if (adjacent) {
+            if (lane == 0) bulk_load_1d(dst, base + (size_t)p_idx[r0] * p.hidden, (uint32_t)(n * rb), &full_bar[s]);
+          } else if (lane < n) {
+            bulk_load_1d(dst + (size_t)lane * rb, base + (size_t)p_idx[r0 + lane] * p.hidden, (uint32_t)rb, &full_bar[s]);
+          }
+        } else if (lane == 0) {
+          mbar_arrive(&full_bar[s]);   // an empty stage: all-masked chunk, or the end marker
+        }
+        if (++s == p.n_stages) { s = 0; ph ^= 1; }
+      }
+      if (done) break;
+    }
+  } else {
+    // ===== consumers =====
+    const int g = t / C, col = t - g * C;
+    const bool active = g < groups;
+    const int n_tail_warps = (C + 31) / 32;          // warps that hold the C finishing threads
+    float acc[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) acc[e] = 0.f;
+    int s = 0, buf = 0;
+    uint32_t ph = 0;
+    Tout* out = static_cast<Tout*>(p.out);
+    for (;;) {
+      mbar_wait(&full_bar[s], ph);
+      const PoolStageMeta* mt = &meta[s];
+      const int n = mt->n_rows;
+      if (n < 0) break;
+      const int last = mt->last;
+      const long long chunk = mt->chunk;
+      const float wsum = mt->wsum;
+      if (active) {
+        const unsigned char* rows = stages + (size_t)s * stage_bytes + (size_t)col * (8 * sizeof(Tin));
+        for (int r = g; r < n; r += groups) {
+          const float w = mt->w[r];
+          float f[8];
+          if constexpr (sizeof(Tin) == 2) {
+            const uint4 v = *reinterpret_cast<const uint4*>(rows + (size_t)r * rb);
+            Elem<Tin>::unpack(v, f);
+          } else {
+            const uint4 a = *reinterpret_cast<const uint4*>(rows + (size_t)r * rb);
+            const uint4 b2 = *reinterpret_cast<const uint4*>(rows + (size_t)r * rb + 16);
+            Elem<float>::unpack(a, f); Elem<float>::unpack(b2, f + 4);
+          }
+#pragma unroll
+          for (int e = 0; e < 8; ++e) acc[e] = fmaf(w, f[e], acc[e]);
+        }
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&empty_bar[s]);     // this warp is done with the stage
+      if (++s == p.n_stages) { s = 0; ph ^= 1; }
+      if (last) {
+        float* ab = accs + (size_t)buf * groups * C * 8;
+        if (active) {
+#pragma unroll
+          for (int e = 0; e < 8; ++e) ab[((size_t)g * C + col) * 8 + e] = acc[e];
+        }
+#pragma unroll
+        for (int e = 0; e < 8; ++e) acc[e] = 0.f;
+        named_bar_sync_pool(1, kPoolRingConsumers);  // every group's partial sums are in shared memory
+        if (warp < n_tail_warps) {
+          float v[8];
+          float ss = 0.f;
+          const float inv_cnt = 1.0f / fmaxf(wsum, 1e-9f);
+          if (t < C) {
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+              float sum = 0.f;
+              for (int gg = 0; gg < groups; ++gg) sum += ab[((size_t)gg * C + t) * 8 + e];
+              v[e] = sum * inv_cnt;
+              ss = fmaf(v[e], v[e], ss);
+            }
+          }
+          ss = warp_sum(ss);
+          if (lane == 0) red[buf * 4 + warp] = ss;
+          named_bar_sync_pool(2, n_tail_warps * 32);
+          float tot = 0.f;
+          for (int w2 = 0; w2 < n_tail_warps; ++w2) tot += red[buf * 4 + w2];
+          const float nrm = sqrtf(tot);
+          const float den = fmaxf(nrm, 1e-12f);
+          if (t < C) {
+#pragma unroll
+            for (int e = 0; e < 8; ++e) v[e] = __fdiv_rn(v[e], den);
+            store8_packed(out + chunk * p.ld_out, t, v);
+          }
+          if (t == 0 && p.norms) p.norms[chunk] = nrm;
+        }
+        buf ^= 1;
+      }
+    }
+  }
 }
 
 }  // namespace ragb

@@ -5,6 +5,7 @@
 // `const void*` entry points and launches them with cudaLaunchKernel / cudaLaunchKernelExC, so editing host logic
 // never recompiles a kernel.  The argument lists are the kernels' own (see the .cuh each getter names).
 #pragma once
+#include <cstddef>
 
 namespace ragb {
 
@@ -37,6 +38,8 @@ const void* k_scan_generic(int dtype, int* rows_per_warp_iter);
 // ingest.cuh
 const void* k_norm_pack(int tin, int tout, int G, int cpl);   // norm_pack_sub_kernel<Tin,Tout,G,cpl>; G == 0: norm_pack_kernel (any length)
 const void* k_pool(int tin, int tm, int tout);         // pool_norm_pack_kernel<Tin,Tm,Tout>
+const void* k_pool_ring(int tin, int tm, int tout);    // pool_ring_kernel<Tin,Tm,Tout>(PoolRingParams)
+size_t pool_ring_smem_bytes(int tin, int n_stages, int seq, int hidden);
 int pool_threads();
 
 }  // namespace ragb

@@ -186,4 +186,40 @@ struct FilterParams {
 // ---- rank.cuh --------------------------------------------------------------------------------------------
 constexpr int kRankThreads = 256;
 
+// ---- ingest.cuh (pool_ring_kernel) ----------------------------------------------------------------------
+#ifndef RAGB_POOL_RING_ROWS
+#define RAGB_POOL_RING_ROWS 16  // token rows per ring stage (build-time A/B)
+#endif
+constexpr int kPoolRingRows = RAGB_POOL_RING_ROWS;
+constexpr int kPoolRingConsumers = 256;
+constexpr int kPoolRingThreads = kPoolRingConsumers + 32;
+struct PoolStageMeta {
+  int n_rows;      // < 0: no more chunks
+  int last;        // last stage of its chunk
+  long long chunk;
+  float wsum;      // valid in the last stage: sum of ALL mask weights of the chunk
+  float w[kPoolRingRows];
+};
+struct PoolRingParams {
+  const void* tok;
+  const void* mask;
+  long long batch;
+  int seq, hidden;
+  void* out;
+  long long ld_out;
+  float* norms;
+  unsigned long long* counter;  // zero before the launch
+  int n_stages;
+};
+// dynamic shared memory: stages [n_stages][16][row bytes] | meta [n_stages] | full/empty barriers | producer list
+// (int idx[seq] | float w[seq]) | accs [2][groups][C][8] | red [8]
+template <typename Tin>
+__host__ __device__ inline size_t pool_ring_smem(int n_stages, int seq, int hidden) {
+  const size_t rb = (size_t)hidden * sizeof(Tin);
+  const int C = hidden / 8, groups = kPoolRingConsumers / C;
+  return (size_t)n_stages * kPoolRingRows * rb + (size_t)n_stages * sizeof(PoolStageMeta) + (size_t)n_stages * 16 +
+         (size_t)((seq + 3) / 4 * 4) * 8 + (size_t)2 * groups * C * 8 * 4 + 64 + 128;
+}
+
+
 }  // namespace ragb
