@@ -557,10 +557,22 @@ static bool cpl_ok(int c) { return c == 1 || c == 2 || c == 3 || c == 4 || c == 
 
 static int scan_launch(ragb_store* s, const ScanParams& p, int64_t nq, cudaStream_t st, int* n_lists) {
   const int chunks = (int)(p.ld * elem_size(s->dtype) / 16);
+  // Lanes per row: the FEWEST lanes whose share of a row is an instantiated chunk count (<= 8 x 16 B).  The loads in
+  // flight per lane are the same either way (scan_unroll), but a row then costs log2(G) shuffle steps over fewer lanes:
+  // 10M x 768 fp16, batch 1: G=16 x 6 chunks 6 949 GB/s against G=32 x 3 chunks 6 180; 384: G=8 x 6 7 021 against
+  // G=16 x 3 6 415 (profiles/r2_scan_lanes_ab.txt).  RAGB_SCAN_G=<8|16|32> forces a width, RAGB_SCAN_WIDE=1 is the old
+  // widest-first choice — both for A/B runs.
   int bestG = 0;
-  for (int pass = 0; pass < 2 && !bestG; ++pass)
-    for (int G = 32; G >= 8; G >>= 1)
-      if (chunks % G == 0 && cpl_ok(chunks / G) && (pass == 1 || chunks / G >= 2)) { bestG = G; break; }
+  static const int wide = env_int("RAGB_SCAN_WIDE", 0), force = env_int("RAGB_SCAN_G", 0);
+  if (wide) {
+    for (int pass = 0; pass < 2 && !bestG; ++pass)
+      for (int G = 32; G >= 8; G >>= 1)
+        if (chunks % G == 0 && cpl_ok(chunks / G) && (pass == 1 || chunks / G >= 2)) { bestG = G; break; }
+  } else {
+    for (int G = 8; G <= 32; G <<= 1)
+      if (chunks % G == 0 && cpl_ok(chunks / G)) { bestG = G; break; }
+  }
+  if (force && chunks % force == 0 && cpl_ok(chunks / force)) bestG = force;
   int R = 0;
   const void* kern = bestG ? k_scan(s->dtype, bestG, chunks / bestG, &R) : nullptr;
   const bool generic = kern == nullptr;
