@@ -139,6 +139,33 @@ int ragb_search_dev(ragb_store* s, const float* q, int64_t nq, int k, int metric
                     int flags, int64_t row_begin, int64_t row_end, const uint8_t* valid,
                     float* out_scores, int64_t* out_ids, void* stream);
 
+/* ---- search that allocates nothing ---------------------------------------------
+ * No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * ragb_scan_topk_static_dev is the scan search of ragb_search_dev (RAGB_FORCE_SCAN: every row read once, exact fp32
+ * scores, same order among equal scores) over rows the CALLER holds on `device` — packed unit rows as written by
+ * ragb_norm_pack_dev / ragb_store_rows_dev: `n` rows of `dim` elements of `dtype`, row stride `ld` elements
+ * (ld * element size a multiple of 16 bytes, base 16-byte aligned, the padding elements finite) — with the kernel's
+ * scratch (one list of ragb_kpad(k) candidate keys per CTA and query, one ticket word per query) in a file-scope
+ * __device__ array of the library instead of a cudaMalloc'ed workspace: 2 425 088 bytes that every GPU which loads
+ * the library holds until the process exits.  It calls no cudaMalloc / cudaFree / allocating library routine; all
+ * buffers (q [nq][dim] fp32, valid [n] or NULL, out_scores [nq][k], out_ids [nq][k] = row numbers) are device
+ * memory of the caller; the work is queued on `stream` (a cudaStream_t; NULL = the legacy default stream) and
+ * the call returns without synchronising.
+ *   limits  nq <= RAGB_STATIC_SCAN_MAX_NQ and nq * ragb_kpad(k) <= RAGB_STATIC_SCAN_MAX_KEYS per call (e.g. 64
+ *           queries at k <= 16, 8 at k <= 128, 1 at k <= 1024); beyond that: RAGB_EUNSUPPORTED with a message that
+ *           names the limit, nothing launched.  n < 2^32.
+ *   set-up  the first call on a device resolves the array's device address (cudaGetSymbolAddress) — make it before a
+ *           capture starts; a call with nq = 0 does only that.
+ *   sharing every call on a device uses the SAME array: two calls that overlap on the GPU (different streams, or two
+ *           graphs in flight) race on it and return garbage — order them on one stream or with events.  The array
+ *           keeps the last call's contents; the words that must start at zero are cleared on `stream` by every call. */
+#define RAGB_STATIC_SCAN_MAX_NQ 64
+#define RAGB_STATIC_SCAN_MAX_KEYS 1024
+int ragb_scan_topk_static_dev(int device, const void* rows, int dtype, int64_t n, int dim, int64_t ld,
+                              const float* q, int64_t nq, int k, int metric, float threshold, int flags,
+                              const uint8_t* valid, float* out_scores, int64_t* out_ids, void* stream);
+
 /* ---- candidate-set policy on the device ---------------------------------------
  * The SQL of _search_sqlite (ollama_rag_system.py:462-477: WHERE source IN (...) ORDER BY timestamp DESC
  * LIMIT 1000), the NULL-embedding skip (:485-492) and INSERT OR REPLACE (:351), evaluated by kernels over

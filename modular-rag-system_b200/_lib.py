@@ -62,6 +62,7 @@ SIGNATURES = {
     "ragb_store_put_rows": (_i, [_vp, _vp, _vp, _i64, _pi64]),
     "ragb_search": (_i, [_vp, _vp, _i64, _i, _i, _f, _i, _i64, _i64, _vp, _vp, _vp]),
     "ragb_search_dev": (_i, [_vp, _vp, _i64, _i, _i, _f, _i, _i64, _i64, _vp, _vp, _vp, _vp]),
+    "ragb_scan_topk_static_dev": (_i, [_i, _vp, _i, _i64, _i, _i64, _vp, _i64, _i, _i, _f, _i, _vp, _vp, _vp, _vp]),
     "ragb_store_set_meta": (_i, [_vp, _i64, _i64, _vp, _vp]),
     "ragb_store_build_filter": (_i, [_vp, _vp, _i, _i64, _pi64]),
     "ragb_store_set_timestamps": (_i, [_vp, _i64, _i64, _vp]),
