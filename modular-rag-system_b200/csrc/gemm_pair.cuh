@@ -401,14 +401,21 @@ __device__ __forceinline__ void epi_flush(EpiCtx& e, int64_t qrow0, int split, c
 // profiles/r1d_pair_top100_waits.txt); at dim <= 384 a tile's MMA takes 3 072 cycles, the epilogue 2 500 - 3 000, and
 // any prune lands on the critical path (tensor pipe 74 % active at 1M x 384).  Two warps per scheduler overlap those
 // chains, which leaves the TMEM read rate (64 B/cycle: 2 048 cycles per tile) as the epilogue's floor.
-template <int E, int kPairStages, bool kQRes = false, bool kEpi8 = false>
+//
+// kSolo: ONE CTA per SM, no cluster — tcgen05.mma.cta_group::1 of shape M=128 x N=256 x K=16, the CTA stages its query
+// k-block and all 256 corpus rows of a k-block itself (48 KB stages).  For a batch of ONE query tile (4 <= B <= 128): the
+// pair form would run it beside an all-zero query tile, i.e. spend half of every MMA and half of the TMEM reads on
+// nothing.  Such a batch is HBM-bound (128 queries x 2 flop per corpus byte pair), so what matters is corpus bytes in
+// flight per SM — every SM walks its own row split, 32 KB of corpus per stage.  Same epilogue, same keys out.
+template <int E, int kPairStages, bool kQRes = false, bool kEpi8 = false, bool kSolo = false>
 __global__ void __launch_bounds__(kEpi8 ? kPairThreads8 : kGemmThreads, 1)
 gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_x,
                       const TsParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // carve: [resident query k-blocks] | stages | candidate buffers | barriers | tmem base   (identical offsets in both CTAs)
   typedef CandCfg<E, kQRes> Cand;
-  constexpr int kStageB = kQRes ? kStageBytesA : kPairStageBytes;  // bytes per ring stage
+  static_assert(!(kSolo && kQRes), "the solo form streams its query k-blocks");
+  constexpr int kStageB = kSolo ? kStageBytes : kQRes ? kStageBytesA : kPairStageBytes;  // bytes per ring stage
   uint8_t* smem = reinterpret_cast<uint8_t*>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   uint8_t* q_base = smem;
   uint8_t* stage_base = smem + (kQRes ? (size_t)p.n_kb * kStageBytesA : 0);
@@ -426,26 +433,31 @@ gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_co
   float* qs_thr = reinterpret_cast<float*>(qs_sorted + kGemmM);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int rank = blockIdx.x & 1;               // cluster dims (2,1,1): rank == %cluster_ctarank
-  const int pair = blockIdx.x >> 1;
-  const int pps = p.n_qt >> 1;                   // pairs per row split
-  const int split = pair / pps, qt = (pair % pps) * 2 + rank;
+  const int rank = kSolo ? 0 : (int)(blockIdx.x & 1);   // cluster dims (2,1,1): rank == %cluster_ctarank
+  const int pair = kSolo ? (int)blockIdx.x : (int)(blockIdx.x >> 1);
+  const int pps = kSolo ? p.n_qt : p.n_qt >> 1;  // pairs (solo: CTAs) per row split
+  const int split = pair / pps, qt = kSolo ? pair % pps : (pair % pps) * 2 + rank;
   const int64_t t0 = p.n_tiles * split / p.n_splits, t1 = p.n_tiles * (split + 1) / p.n_splits;
   const int n_kb = p.n_kb;
 
   if (threadIdx.x == 0) {
     for (int i = 0; i < kPairStages; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
-    for (int i = 0; i < 2; ++i) { mbar_init(&tfull_bar[i], 1); mbar_init(&tempty_bar[i], kEpi8 ? 16 : 8); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&tfull_bar[i], 1); mbar_init(&tempty_bar[i], (kEpi8 ? 16 : 8) / (kSolo ? 2 : 1)); }
     mbar_init(q_bar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) {  // the same warp of BOTH CTAs allocates for the pair
-    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_base_smem)), "r"(512));
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;");
+    if constexpr (kSolo) {
+      asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_base_smem)), "r"(512));
+      asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+    } else {
+      asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_base_smem)), "r"(512));
+      asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;");
+    }
   }
   tc_fence_before();
   __syncthreads();
-  cluster_sync_all();
+  if constexpr (!kSolo) cluster_sync_all();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_base_smem;
 
@@ -463,7 +475,7 @@ gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_co
       __syncwarp();
     }
     for (int64_t t = t0; t < t1; ++t) {
-      const int row0 = (int)(p.row_begin + t * kPairN) + rank * (kPairN / 2);
+      const int row0 = (int)(p.row_begin + t * kPairN) + (kSolo ? 0 : rank * (kPairN / 2));
       // The pps pairs of a row split read the same rows; nothing else keeps them together, and once they drift
       // further apart than L2 holds, every pair fetches the split from HBM by itself (measured: 22 - 40 GB read for
       // 15.4 GB of corpus).  Every kPairSyncTiles tiles the leaders' producers meet at a counter in global memory;
@@ -480,11 +492,17 @@ gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_co
       for (int kb = 0; kb < n_kb; ++kb) {
         mbar_wait(&empty_bar[s], ph ^ 1);  // the leader's commit released this slot in both CTAs
         if (elect_one()) {
-          if (rank == 0) mbar_expect_tx(&full_bar[s], 2u * kStageB);  // both CTAs' bytes land on the leader
           uint8_t* d = stage_base + (size_t)s * kStageB;
-          if constexpr (kQRes) {
+          if constexpr (kSolo) {  // query k-block | 256 corpus rows as two boxes of 128 (the pair form's tensor map)
+            mbar_expect_tx(&full_bar[s], (uint32_t)kStageB);
+            tma_load_2d(d, &map_q, &full_bar[s], kb * kGemmKB, q_row);
+            tma_load_2d(d + kStageBytesA, &map_x, &full_bar[s], kb * kGemmKB, row0);
+            tma_load_2d(d + 2 * kStageBytesA, &map_x, &full_bar[s], kb * kGemmKB, row0 + kPairN / 2);
+          } else if constexpr (kQRes) {
+            if (rank == 0) mbar_expect_tx(&full_bar[s], 2u * kStageB);  // both CTAs' bytes land on the leader
             tma_load_2d_pair(d, &map_x, &full_bar[s], kb * kGemmKB, row0);
           } else {
+            if (rank == 0) mbar_expect_tx(&full_bar[s], 2u * kStageB);
             tma_load_2d_pair(d, &map_q, &full_bar[s], kb * kGemmKB, q_row);
             tma_load_2d_pair(d + kStageBytesA, &map_x, &full_bar[s], kb * kGemmKB, row0);
           }
@@ -504,7 +522,8 @@ gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_co
         if (t0 < t1) { mbar_wait(q_bar, 0); tc_fence_after(); }
       }
       for (int64_t t = t0; t < t1; ++t) {
-        mbar_wait_cluster(&tempty_bar[acc], aph ^ 1);  // both CTAs' epilogues drained this accumulator
+        if constexpr (kSolo) mbar_wait(&tempty_bar[acc], aph ^ 1);
+        else mbar_wait_cluster(&tempty_bar[acc], aph ^ 1);  // both CTAs' epilogues drained this accumulator
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * (uint32_t)kPairN;
         for (int kb = 0; kb < n_kb; ++kb) {
@@ -514,11 +533,19 @@ gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_co
             const uint64_t sdesc = desc0 + (uint64_t)((uint32_t)s * (kStageB >> 4));
             const uint64_t adesc = kQRes ? descq + (uint64_t)((uint32_t)kb * (kStageBytesA >> 4)) : sdesc;
             const uint64_t bdesc = kQRes ? sdesc : sdesc + (kStageBytesA >> 4);
+            if constexpr (kSolo) {
 #pragma unroll
-            for (int k4 = 0; k4 < kGemmKB / 16; ++k4)
-              tc_mma_f16_pair(d_tmem, adesc + (uint64_t)(k4 * 2), bdesc + (uint64_t)(k4 * 2), idesc, (kb | k4) != 0);
-            tc_commit_pair(&empty_bar[s]);
-            if (kb == n_kb - 1) tc_commit_pair(&tfull_bar[acc]);
+              for (int k4 = 0; k4 < kGemmKB / 16; ++k4)
+                tc_mma_f16(d_tmem, adesc + (uint64_t)(k4 * 2), bdesc + (uint64_t)(k4 * 2), idesc, (kb | k4) != 0);
+              tc_commit(&empty_bar[s]);
+              if (kb == n_kb - 1) tc_commit(&tfull_bar[acc]);
+            } else {
+#pragma unroll
+              for (int k4 = 0; k4 < kGemmKB / 16; ++k4)
+                tc_mma_f16_pair(d_tmem, adesc + (uint64_t)(k4 * 2), bdesc + (uint64_t)(k4 * 2), idesc, (kb | k4) != 0);
+              tc_commit_pair(&empty_bar[s]);
+              if (kb == n_kb - 1) tc_commit_pair(&tfull_bar[acc]);
+            }
           }
           if (++s == kPairStages) { s = 0; ph ^= 1; }
         }
@@ -589,7 +616,10 @@ gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_co
       }
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive_cta(&tempty_bar[acc], 0);
+      if (lane == 0) {
+        if constexpr (kSolo) mbar_arrive(&tempty_bar[acc]);
+        else mbar_arrive_cta(&tempty_bar[acc], 0);
+      }
       if ((acc ^= 1) == 0) aph ^= 1;
       // after the accumulator is handed back: off the MMA's critical path
       if constexpr (kEpi8) epi_prune8<E, kQRes>(e, p, lane, quarter, half);
@@ -601,10 +631,11 @@ gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_co
 
   tc_fence_before();
   __syncthreads();
-  cluster_sync_all();  // neither CTA leaves (or frees TMEM) while the other may still use the pair
+  if constexpr (!kSolo) cluster_sync_all();  // neither CTA leaves (or frees TMEM) while the other may still use the pair
   if (warp == 1) {
     tc_fence_after();
-    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512));
+    if constexpr (kSolo) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512));
+    else asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512));
   }
 }
 

@@ -16,6 +16,8 @@ const void* k_pair_e8(bool qres, bool epi8);
 inline const void* k_pair(int E, bool qres, bool epi8) {
   return E == 2 ? k_pair_e2(qres, epi8) : E == 4 ? k_pair_e4(qres, epi8) : k_pair_e8(qres, epi8);
 }
+// gemm_pair.cuh, kSolo: gemm_topk_pair_kernel<E, stages, false, true, true> — one CTA, M=128, for a batch of one query tile
+const void* k_solo(int E);
 // gemm_ts.cuh / gemm_topk.cuh (single-CTA fallbacks), query conversion, fp32 re-score
 const void* k_ts(bool ts);                  // gemm_topk_ts_kernel<ts>(map_q, map_x, TsParams)
 const void* k_gemm_topk();                  // gemm_topk_kernel(map_q, map_x, GemmParams)

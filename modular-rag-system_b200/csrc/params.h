@@ -86,6 +86,10 @@ constexpr int kPairSyncTiles = 8;                 // default tiles between two m
 constexpr int kPairCapSmall = 64;
 constexpr int kPairCapSmallQ = 48;  // next to a resident query tile: k <= 32 survivors + the 16 chunks one tile can add
 
+// solo form (one CTA, cta_group::1, a batch of one query tile): 48 KB stages = 16 KB query k-block + 32 KB corpus k-block
+constexpr int kSoloStagesSmall = 3;    // next to the 65 KB of shared-memory candidate buffers (kpad <= 32)
+constexpr int kSoloStagesLarge = 4;    // kpad 64 / 128: candidates live in global memory
+
 constexpr int kPairQResMaxKB = 6;
 constexpr int kPairStagesSmallQ = 5;   // x 16 KB, next to 96 KB of queries and the 49 KB of candidate buffers
 constexpr int kPairStagesLargeQ = 8;   // x 16 KB, next to 96 KB of queries

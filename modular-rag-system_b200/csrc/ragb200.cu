@@ -836,6 +836,68 @@ static int gemm_pair_launch(ragb_store* s, SearchCtx* c, const SearchReq& r, cud
   return gemm_finish_chunks(s, r, kpad, k_sel, p.out, splits, st);
 }
 
+// One query tile (4 <= B <= 128) on every SM by itself (gemm_pair.cuh: kSolo): tcgen05.mma.cta_group::1, M=128 x N=256,
+// every CTA walks its own row split.  The batch is HBM-bound (one pass over the rows), so the grid is one CTA per SM.
+static int gemm_solo_launch(ragb_store* s, SearchCtx* c, const SearchReq& r, cudaStream_t st) {
+  GemmShared* g = &s->gemm;
+  const int kpad = kpad_of(r.k);
+  const int n_kb = (s->dim + kGemmKB - 1) / kGemmKB;
+  if ((r.flags & RAGB_NO_RESCORE) || kpad > 128 || r.nq > kGemmM) return RAGB_EUNSUPPORTED;
+  const int64_t nq_pad = kGemmM;
+  const int E = kpad <= 32 ? 2 : kpad == 64 ? 4 : 8;
+  const int n_stages = E == 2 ? kSoloStagesSmall : kSoloStagesLarge;
+  const size_t cand_stride = E == 2 ? kPairCapSmall + 1 : 32 * E;
+  const size_t smem = 1024 + (size_t)n_stages * kStageBytes + (E == 2 ? (size_t)kGemmM * cand_stride * 8 : 0) +
+                      (2 * n_stages + 5) * 8 + 16 + (E == 2 ? 0 : 16 + 3 * kGemmM * 4);
+  const void* kern = k_solo(E);
+  const int ei = E == 2 ? 0 : E == 4 ? 1 : 2;
+  CUtensorMap map_x, map_q;
+  {
+    std::lock_guard<std::mutex> lk(g->mu);
+    if (g->pair_rows != s->rows || g->pair_capacity != s->capacity) {   // the pair form's map: boxes of 128 rows
+      RB_TRY(make_map(g, &g->map_x_pair, s->dtype, s->rows, s->dim, s->capacity, s->ld, kPairN / 2));
+      g->pair_rows = s->rows; g->pair_capacity = s->capacity;
+    }
+    map_x = g->map_x_pair;
+    if (!g->solo_attr[ei]) {
+      CU_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      g->solo_attr[ei] = true;
+    }
+    RB_TRY(convert_queries(s, c, r, nq_pad, st));
+    RB_TRY(make_map(g, &map_q, s->dtype, c->qh, s->dim, nq_pad, s->ld, kGemmM));
+  }
+  TsParams p = {};
+  p.qh = c->qh; p.ld_q = s->ld; p.n_kb = n_kb; p.nt = kPairN; p.kbs = 1; p.stages = n_stages; p.cluster = 1;
+  p.row_begin = r.rb; p.row_end = r.re; p.valid = r.valid; p.nq = r.nq; p.n_qt = 1;
+  p.n_tiles = (r.re - r.rb + kPairN - 1) / kPairN;
+  // a CTA's first tiles run with loose thresholds: give every CTA at least a few tiles before adding CTAs
+  int splits = (int)std::min<int64_t>(s->n_sm, std::max<int64_t>(1, p.n_tiles / 4));
+  p.n_splits = splits;
+  const int k_sel = kpad;
+  p.flags = r.flags; p.threshold = r.threshold; p.k = k_sel; p.kpad = kpad;
+  p.sel_slack = s->dtype == RAGB_BF16 ? 8e-3f : 2e-3f;
+  p.id_base = 0;
+  p.idesc = umma_idesc(s->dtype == RAGB_BF16, kGemmM, kPairN);
+  p.sync_ctr = nullptr;
+  const size_t part_bytes = (size_t)nq_pad * splits * kpad * sizeof(uint64_t);
+  const size_t cand_bytes = E == 2 ? 0 : (size_t)splits * kGemmM * (32 * E) * sizeof(uint64_t);
+  const size_t gthr_bytes = (splits > 1 && env_int("RAGB_PAIR_GTHR", 1)) ? (size_t)nq_pad * sizeof(unsigned) : 0;
+  RB_TRY(grow(&c->ws, &c->ws_bytes, part_bytes + cand_bytes + gthr_bytes, false));
+  p.out = (uint64_t*)c->ws;
+  p.cand_ws = E == 2 ? nullptr : (uint64_t*)((char*)c->ws + part_bytes);
+  p.gthr = nullptr;
+  p.full_sort = env_int("RAGB_PAIR_FULLSORT", 0);
+  if (gthr_bytes) {
+    p.gthr = (unsigned*)((char*)c->ws + part_bytes + cand_bytes);
+    CU_TRY(cudaMemsetAsync(p.gthr, 0, gthr_bytes, st));
+  }
+  {
+    ProfScope prof(s, st);
+    LAUNCH(kern, dim3((unsigned)splits), dim3(kPairThreads8), smem, st, map_q, map_x, p);
+  }
+  return gemm_finish_chunks(s, r, kpad, k_sel, p.out, splits, st);
+}
+
 // A batch of `pairs` query-tile pairs runs as floor(P / pairs) row splits on the P SM pairs of the device; when that
 // leaves pairs idle (16 tile pairs -> 4 splits -> 64 of 74), the batch can be cut into equal groups that fill the
 // device better (2 x 8 tile pairs -> 9 splits -> 72 of 74).  Measured on B200 (12.5M x 384 bf16, B=4096): top-100,
@@ -973,8 +1035,13 @@ static int gemm_ts_search(ragb_store* s, SearchCtx* c, const SearchReq& r, cudaS
 }
 
 static int gemm_search(ragb_store* s, SearchCtx* c, const SearchReq& r, cudaStream_t st) {
+  if (pair_enabled() && r.nq <= kGemmM && env_int("RAGB_SOLO", 1)) {
+    // One query tile (B <= 128): its own kernel form — one CTA per SM, M=128, nothing spent on a zero tile
+    int rc = gemm_solo_launch(s, c, r, st);
+    if (rc != RAGB_EUNSUPPORTED) return rc;
+  }
   if (pair_enabled()) {
-    // One query tile (B <= 128): the pair kernel runs it beside an all-zero tile, i.e. at half its tensor rate, but its
+    // (RAGB_SOLO=0) One query tile (B <= 128): the pair kernel runs it beside an all-zero tile, i.e. at half its tensor rate, but its
     // chunk-granular epilogue has no warm-up; the single-CTA kernel wastes nothing and streams at ~85 % of HBM peak, but
     // pays ~0.4 ms of row-granular insertions while thresholds are loose.  Measured crossover: N*D around 8e9
     // (1M x 384, B=128: 0.27 vs 0.64 ms; 10M x 768: 2.99 vs 2.90 ms).  RAGB_PAIR_SMALL=0/1 forces either.

@@ -96,6 +96,7 @@ struct GemmShared {
   const void* pair_rows = nullptr; int64_t pair_capacity = -1;
   int pair_clusters[12] = {};
   bool pair_attr[12] = {};
+  bool solo_attr[3] = {};
   bool ts_attr[2] = {false, false};
   bool ss_attr = false;
   int occ_c = 0, occ_clusters = 0;

@@ -131,35 +131,67 @@ def test_batched_policy_flags():
 # full-size (1M x 384, 10M x 768, 12.5M x 384) parity against the float64 oracle: tests/test_fullsize_parity_gpu.py
 
 
-@pytest.mark.parametrize("nq,k", [(4, 10), (17, 5), (128, 32), (40, 100), (2, 64)])
-def test_single_tile_batches_on_both_kernels(nq, k, monkeypatch):
-    """B <= 128 is one query tile: below the measured crossover it runs on the SM-pair kernel beside an all-zero tile
-    (chunk-granular epilogue), above it on the single-CTA kernel (csrc/ragb200.cu, gemm_search).  Both must agree with
-    the oracle; RAGB_PAIR_SMALL forces either.  k > 32 exists only on the pair kernel."""
+@pytest.mark.parametrize("nq,k,dim,dtype", [(4, 10, 384, "fp16"), (17, 5, 384, "fp16"), (128, 32, 384, "fp16"), (40, 100, 384, "fp16"),
+                                            (2, 64, 384, "fp16"), (128, 10, 768, "bf16"), (77, 16, 100, "fp16"), (128, 128, 1024, "fp16")])
+def test_single_tile_batches_on_every_kernel(nq, k, dim, dtype, monkeypatch):
+    """B <= 128 is one query tile.  Default: the solo form of the tcgen05 kernel (one CTA per SM, cta_group::1, M=128 —
+    csrc/gemm_pair.cuh kSolo).  RAGB_SOLO=0 brings back the earlier routing: below the measured crossover the SM-pair
+    kernel beside an all-zero tile, above it the single-CTA row-granular kernel (RAGB_PAIR_SMALL forces either; k > 32
+    exists only on the chunk-granular kernels).  All must agree with the oracle; solo and pair end in the same fp32
+    re-score, so they must return the same rows and bit-identical scores."""
     import modular_rag_system_b200 as pkg
     FORCE_GEMM, _, _ = _flags()
     rng = np.random.default_rng(nq * 1000 + k)
-    n, dim = 30000, 384
+    n = 30000
     X = rng.standard_normal((n, dim)).astype(np.float32)
+    X[29990] = X[15000] = X[4321]                # exact ties across row splits
     Q = rng.standard_normal((nq, dim)).astype(np.float32)
     Q[0] = X[4321] + 0.3 * rng.standard_normal(dim).astype(np.float32)
-    s = _store(X, "fp16")
+    s = _store(X, dtype)
     got = {}
-    for force in ("1", "0"):
-        monkeypatch.setenv("RAGB_PAIR_SMALL", force)
+    for route, env in (("solo", {}), ("pair", {"RAGB_SOLO": "0", "RAGB_PAIR_SMALL": "1"}),
+                       ("single", {"RAGB_SOLO": "0", "RAGB_PAIR_SMALL": "0"})):
+        for name, v in env.items():
+            monkeypatch.setenv(name, v)
         l0 = pkg.launch_count()
         ids, sc = s.search(Q, k, "cosine", flags=FORCE_GEMM)
         launches = pkg.launch_count() - l0
-        _check(ids, sc, X, Q, k, "cosine", -np.inf, False, TOL["fp16"])
-        assert ids[0][0] == 4321
-        got[force] = (ids, sc, launches)
-    assert got["1"][2] == 3                      # convert + pair kernel + finish
+        _check(ids, sc, X, Q, k, "cosine", -np.inf, False, TOL[dtype])
+        assert list(ids[0][:3]) == [29990, 15000, 4321]
+        got[route] = (np.array(ids), np.array(sc), launches)
+        for name in env:
+            monkeypatch.delenv(name)
+    assert got["solo"][2] == 3 and got["pair"][2] == 3      # convert + tcgen05 kernel + finish
+    np.testing.assert_array_equal(got["solo"][0], got["pair"][0])
+    np.testing.assert_array_equal(got["solo"][1], got["pair"][1])
     if k <= 32:
-        assert got["0"][2] > 3                   # convert + single-CTA kernel + merge + re-score + merge
-        np.testing.assert_allclose(got["0"][1], got["1"][1], atol=2e-3)
-    monkeypatch.delenv("RAGB_PAIR_SMALL")
-    ids, sc = s.search(Q, k, "cosine")           # default routing
-    _check(ids, sc, X, Q, k, "cosine", -np.inf, False, TOL["fp16"])
+        assert got["single"][2] > 3              # convert + single-CTA kernel + merge + re-score + merge
+        np.testing.assert_allclose(got["single"][1], got["solo"][1], atol=2e-3)
+    s.close()
+
+
+@pytest.mark.parametrize("nq,k", [(128, 10), (33, 100)])
+def test_solo_masked_epilogue_window_and_threshold(nq, k):
+    """The solo form under a valid mask, a row window that ends inside a tile, a score threshold and clamp — against the
+    scan path (exact fp32, same re-score arithmetic)."""
+    FORCE_GEMM, FORCE_SCAN, _ = _flags()
+    rng = np.random.default_rng(k + nq)
+    n, dim = 50_000, 256
+    X = rng.standard_normal((n, dim)).astype(np.float32)
+    Q = rng.standard_normal((nq, dim)).astype(np.float32)
+    for i in range(0, nq, 5):
+        Q[i] = X[(i * 797) % n] + 0.4 * rng.standard_normal(dim).astype(np.float32)
+    valid = (rng.random(n) > 0.3).astype(np.uint8)
+    s = _store(X, "fp16")
+    for kw in (dict(valid=valid), dict(row_begin=1000, row_end=40_001), dict(threshold=0.05, clamp01=True),
+               dict(valid=valid, row_begin=37, row_end=49_999, threshold=0.0, clamp01=True)):
+        a = s.search(Q, k, "cosine", flags=FORCE_GEMM, **kw)
+        b = s.search(Q, k, "cosine", flags=FORCE_SCAN, **kw)
+        same = np.array(a[0]) == np.array(b[0])
+        assert same.mean() > 0.999, kw                       # 16-bit-query selection: a near-tie at the cut may differ
+        fin = same & np.isfinite(np.array(b[1]))
+        assert np.abs(np.array(a[1])[fin] - np.array(b[1])[fin]).max() < 2e-6
+    s.close()
 
 
 @pytest.mark.parametrize("dim,nq,k", [(384, 300, 10), (256, 700, 100), (320, 130, 32), (100, 260, 64)])
