@@ -23,6 +23,24 @@
 
 namespace ragb {
 
+// -DRAGB_PAIR_STATS (build variant, scripts/pair_stats.sh): where the warps of a CTA wait, in cycles, per CTA:
+// [0] kernel  [1] producer: empty slot  [2] producer: meeting  [3] MMA: accumulator free  [4] MMA: stage full
+// [5] epilogue warp 2: accumulator full  [6] epilogue warp 2: prune  [7] epilogue warp 2: flush
+#ifdef RAGB_PAIR_STATS
+#define STAT_T0() const long long st_t0_ = clock64()
+#define STAT_ADD(i) st_acc_[i] += clock64() - st_t0_
+#define STAT_DECL() long long st_acc_[8] = {0, 0, 0, 0, 0, 0, 0, 0}; const long long st_k0_ = clock64()
+#define STAT_OUT(cond, lo, hi)                                                                   \
+  if ((cond) && p.stats) {                                                                       \
+    for (int i_ = (lo); i_ <= (hi); ++i_) p.stats[(size_t)blockIdx.x * 8 + i_] = st_acc_[i_];   \
+  }
+#else
+#define STAT_T0()
+#define STAT_ADD(i)
+#define STAT_DECL()
+#define STAT_OUT(cond, lo, hi)
+#endif
+
 constexpr uint32_t kPeerBitMask = 0xFEFFFFFFu;    // shared::cluster address of the even (leader) CTA of a pair
 
 __device__ __forceinline__ void tma_load_2d_pair(void* dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1) {
@@ -439,6 +457,7 @@ gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_co
   const int split = pair / pps, qt = kSolo ? pair % pps : (pair % pps) * 2 + rank;
   const int64_t t0 = p.n_tiles * split / p.n_splits, t1 = p.n_tiles * (split + 1) / p.n_splits;
   const int n_kb = p.n_kb;
+  STAT_DECL();
 
   if (threadIdx.x == 0) {
     for (int i = 0; i < kPairStages; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
@@ -482,15 +501,17 @@ gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_co
       // the ring is full at that point, so the tensor pipe keeps running while they wait.  Only enabled by the
       // host when every CTA of the grid is resident at once.
       if (p.sync_ctr != nullptr && rank == 0 && t > t0 && ((t - t0) % p.sync_tiles) == 0) {
+        { STAT_T0();
         if (elect_one()) {
           const unsigned target = (unsigned)pps * (unsigned)((t - t0) / p.sync_tiles);
           atomicAdd(&p.sync_ctr[split], 1u);
           while (*reinterpret_cast<volatile unsigned*>(&p.sync_ctr[split]) < target) __nanosleep(64);
         }
         __syncwarp();
+        STAT_ADD(2); }
       }
       for (int kb = 0; kb < n_kb; ++kb) {
-        mbar_wait(&empty_bar[s], ph ^ 1);  // the leader's commit released this slot in both CTAs
+        { STAT_T0(); mbar_wait(&empty_bar[s], ph ^ 1); STAT_ADD(1); }  // the leader's commit released this slot in both CTAs
         if (elect_one()) {
           uint8_t* d = stage_base + (size_t)s * kStageB;
           if constexpr (kSolo) {  // query k-block | 256 corpus rows as two boxes of 128 (the pair form's tensor map)
@@ -510,6 +531,7 @@ gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_co
         if (++s == kPairStages) { s = 0; ph ^= 1; }
       }
     }
+    STAT_OUT(lane == 0, 1, 2);
   } else if (warp == 1) {
     // ===== MMA issuer (leader only): M=256 across the pair =====
     if (rank == 0) {
@@ -522,12 +544,14 @@ gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_co
         if (t0 < t1) { mbar_wait(q_bar, 0); tc_fence_after(); }
       }
       for (int64_t t = t0; t < t1; ++t) {
+        { STAT_T0();
         if constexpr (kSolo) mbar_wait(&tempty_bar[acc], aph ^ 1);
         else mbar_wait_cluster(&tempty_bar[acc], aph ^ 1);  // both CTAs' epilogues drained this accumulator
+        STAT_ADD(3); }
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * (uint32_t)kPairN;
         for (int kb = 0; kb < n_kb; ++kb) {
-          mbar_wait(&full_bar[s], ph);
+          { STAT_T0(); mbar_wait(&full_bar[s], ph); STAT_ADD(4); }
           tc_fence_after();
           if (elect_one()) {
             const uint64_t sdesc = desc0 + (uint64_t)((uint32_t)s * (kStageB >> 4));
@@ -551,6 +575,7 @@ gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_co
         }
         if ((acc ^= 1) == 0) aph ^= 1;
       }
+      STAT_OUT(lane == 0, 3, 4);
     }
   } else {
     // ===== epilogue (both CTAs): thread == query (kEpi8: two threads per query, half of the columns each) =====
@@ -586,7 +611,7 @@ gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_co
     for (int64_t t = t0; t < t1; ++t) {
       const int64_t row0 = p.row_begin + t * kPairN;
       const unsigned gv = e.gthr ? ld_relaxed_u32(e.gthr) : 0u;
-      mbar_wait(&tfull_bar[acc], aph);
+      { STAT_T0(); mbar_wait(&tfull_bar[acc], aph); STAT_ADD(5); }
       tc_fence_after();
       if (gv) e.fthr = fmaxf(e.fthr, unorder_bits(gv));
       const uint32_t taddr = lane_base + acc * (uint32_t)kPairN;
@@ -622,13 +647,21 @@ gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_co
       }
       if ((acc ^= 1) == 0) aph ^= 1;
       // after the accumulator is handed back: off the MMA's critical path
+      { STAT_T0();
       if constexpr (kEpi8) epi_prune8<E, kQRes>(e, p, lane, quarter, half);
       else epi_prune<E, kQRes>(e, p, lane);
+      STAT_ADD(6); }
     }
+    { STAT_T0();
     if constexpr (kEpi8) epi_flush<E, kQRes>(e, (int64_t)qt * kGemmM + quarter * 32, split, p, lane, half, 2, true);
     else epi_flush<E, kQRes>(e, (int64_t)qt * kGemmM + quarter * 32, split, p, lane);
+    STAT_ADD(7); }
+    STAT_OUT(warp == 2 && lane == 0, 5, 7);
   }
 
+#ifdef RAGB_PAIR_STATS
+  if (threadIdx.x == 0 && p.stats) p.stats[(size_t)blockIdx.x * 8] = clock64() - st_k0_;
+#endif
   tc_fence_before();
   __syncthreads();
   if constexpr (!kSolo) cluster_sync_all();  // neither CTA leaves (or frees TMEM) while the other may still use the pair

@@ -71,6 +71,9 @@ struct TsParams {
   int sync_tiles;       // pair kernel: tiles between two meetings
   int full_sort;        // pair kernel, k > 32: 1 = every prune sorts the whole buffer (A/B switch RAGB_PAIR_FULLSORT)
   unsigned* gthr;       // pair kernel: [n_qt*128] zeroed per launch, or null — running threshold shared by the row splits
+#ifdef RAGB_PAIR_STATS
+  long long* stats;     // [grid][8] cycle counters (build variant -DRAGB_PAIR_STATS only; scripts/pair_stats.sh)
+#endif
   unsigned* sync_ctr;   // pair kernel: [n_splits] zeroed per launch, or null — the SM pairs that stream the same row
                         // split meet every kPairSyncTiles tiles so that they keep hitting each other's rows in L2
 };

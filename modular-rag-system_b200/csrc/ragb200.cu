@@ -810,6 +810,12 @@ static int gemm_pair_launch(ragb_store* s, SearchCtx* c, const SearchReq& r, cud
     CU_TRY(cudaMemsetAsync(p.gthr, 0, gthr_bytes, st));
   }
   cfg.gridDim = dim3((unsigned)(n_qt * splits));
+#ifdef RAGB_PAIR_STATS
+  static long long* stats_dev = nullptr;   // build variant only (scripts/pair_stats.sh): one device, one search at a time
+  if (!stats_dev) CU_TRY(cudaMalloc(&stats_dev, 1024 * 8 * sizeof(long long)));
+  CU_TRY(cudaMemsetAsync(stats_dev, 0, 1024 * 8 * sizeof(long long), st));
+  p.stats = stats_dev;
+#endif
   void* args[] = {(void*)&map_q, (void*)&map_x, (void*)&p};
   {
     ProfScope prof(s, st);
@@ -833,6 +839,28 @@ static int gemm_pair_launch(ragb_store* s, SearchCtx* c, const SearchReq& r, cud
   }
   count_launch();
   CU_TRY(cudaGetLastError());
+#ifdef RAGB_PAIR_STATS
+  if (env_int("RAGB_PAIR_STATS_PRINT", 0)) {
+    static std::vector<long long> h(1024 * 8);
+    CU_TRY(cudaStreamSynchronize(st));
+    CU_TRY(cudaMemcpy(h.data(), stats_dev, h.size() * sizeof(long long), cudaMemcpyDeviceToHost));
+    const int grid = n_qt * splits;
+    double sum[8] = {}, mx[8] = {};
+    for (int b = 0; b < grid; ++b)
+      for (int i = 0; i < 8; ++i) {
+        if ((i == 3 || i == 4) && (b & 1)) continue;   // the MMA warp works in the leader only
+        sum[i] += (double)h[b * 8 + i]; mx[i] = std::max(mx[i], (double)h[b * 8 + i]);
+      }
+    static const char* names[8] = {"kernel", "producer: empty slot", "producer: meeting", "MMA: accumulator free", "MMA: stage full",
+                                   "epilogue: accumulator full", "epilogue: prune", "epilogue: flush"};
+    fprintf(stderr, "pair stats: grid %d, E %d, qres %d, tiles per CTA %lld\n", grid, E, (int)qres, (long long)(p.n_tiles / splits));
+    for (int i = 0; i < 8; ++i) {
+      const double n = (i == 3 || i == 4) ? grid / 2 : grid;
+      fprintf(stderr, "  %-28s mean %12.0f cycles (%5.1f %% of the kernel)  max %12.0f\n", names[i], sum[i] / n,
+              100.0 * (sum[i] / n) / (sum[0] / grid), mx[i]);
+    }
+  }
+#endif
   return gemm_finish_chunks(s, r, kpad, k_sel, p.out, splits, st);
 }
 
