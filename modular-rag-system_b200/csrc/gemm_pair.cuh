@@ -245,6 +245,69 @@ __device__ __forceinline__ uint64_t warp_prune(uint64_t* base, int n, int k, int
   }
 }
 
+// Prune by SELECTION instead of sorting (p.full_sort == 2): the epilogue only needs the k best keys of a
+// buffer and the k-th of them as its new threshold — not their order (the flush sorts once, at the end).  The k-th
+// largest of the n <= 32*E keys is found by bisection on the 64-bit key value: every lane holds E keys in registers,
+// one step is E compares and one redux.sync; keys are unique (low word = chunk start row), and the search stops as soon
+// as a pivot separates exactly k keys — typically after 12-16 steps, since the keys of a buffer share their sign and
+// exponent bits.  Survivors are compacted to the front with ballots, unsorted.  About a tenth of the instructions of
+// the 256-key bitonic sort + merge (profiles/r2_pair_wait_stats.txt: the sort-based prune was 14 % / 50 % of an epilogue
+// warp's time at 12.5M x 384 / 1M x 384 top-100).
+template <int E>
+__device__ __forceinline__ uint64_t warp_prune_select(uint64_t* base, int n, int k, int lane, int* keep_out) {
+  uint64_t v[E];
+#pragma unroll
+  for (int e = 0; e < E; ++e) v[e] = (e * 32 + lane < n) ? base[e * 32 + lane] : 0ull;
+  if (n <= k) {   // nothing to drop; the k-th best exists only when n == k
+    *keep_out = n;
+    if (n < k) return 0ull;
+    uint64_t m = ~0ull;
+#pragma unroll
+    for (int e = 0; e < E; ++e) m = (v[e] != 0ull && v[e] < m) ? v[e] : m;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) { const uint64_t t = __shfl_xor_sync(0xffffffffu, m, o); m = t < m ? t : m; }
+    return m;
+  }
+  // bounds from the score words: lo = smallest present key's score word, hi = largest
+  unsigned hmax = 0u, hmin = 0xffffffffu;
+#pragma unroll
+  for (int e = 0; e < E; ++e) {
+    const unsigned h = (unsigned)(v[e] >> 32);
+    hmax = h > hmax ? h : hmax;
+    hmin = (v[e] != 0ull && h < hmin) ? h : hmin;
+  }
+  hmax = __reduce_max_sync(0xffffffffu, hmax);
+  hmin = __reduce_min_sync(0xffffffffu, hmin);
+  uint64_t lo = (uint64_t)hmin << 32, hi = ((uint64_t)hmax << 32) | 0xffffffffull;
+  // invariant: count(v >= lo) >= k (all n > k keys are >= lo), count(v > hi) == 0
+  uint64_t cut = lo;
+  while (lo < hi) {
+    const uint64_t mid = lo + ((hi - lo) >> 1) + 1ull;
+    int c = 0;
+#pragma unroll
+    for (int e = 0; e < E; ++e) c += v[e] >= mid ? 1 : 0;
+    c = __reduce_add_sync(0xffffffffu, c);
+    if (c >= k) { lo = mid; cut = mid; if (c == k) break; }
+    else hi = mid - 1ull;
+  }
+  if (lo >= hi) cut = lo;   // converged without an exact split: lo is the k-th largest key itself
+  // compact the survivors (exactly k: keys are unique) to the front; every key is in registers already
+  __syncwarp();
+  int off = 0;
+  uint64_t m = ~0ull;
+#pragma unroll
+  for (int e = 0; e < E; ++e) {
+    const bool keep = v[e] >= cut;
+    const unsigned b = __ballot_sync(0xffffffffu, keep);
+    if (keep) { base[off + __popc(b & ((1u << lane) - 1u))] = v[e]; m = v[e] < m ? v[e] : m; }
+    off += __popc(b);
+  }
+  *keep_out = off;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) { const uint64_t t = __shfl_xor_sync(0xffffffffu, m, o); m = t < m ? t : m; }
+  return m;   // the k-th best key
+}
+
 // ---- the fused top-k epilogue: CHUNK-granular selection -----------------------------------------
 // Thread == query holds the scores of its query against 32 consecutive rows (two chunks of 16).  The epilogue
 // keeps, per query, the best k_sel CHUNKS (16 consecutive rows) ranked by (chunk maximum, chunk start
@@ -335,7 +398,9 @@ __device__ __forceinline__ void epi_prune(EpiCtx& e, const TsParams& p, int lane
     __syncwarp();
     int keep;
     const int sorted = p.full_sort ? 0 : __shfl_sync(0xffffffffu, e.sorted, j);
-    const uint64_t kth = warp_prune<E>(e.warp_cand + (size_t)j * kStride, n, p.k, lane, &keep, sorted);
+    uint64_t kth;
+    if (p.full_sort == 2) kth = warp_prune_select<E>(e.warp_cand + (size_t)j * kStride, n, p.k, lane, &keep);
+    else kth = warp_prune<E>(e.warp_cand + (size_t)j * kStride, n, p.k, lane, &keep, sorted);
     if (lane == j) {
       e.cnt = keep;
       e.sorted = keep;
@@ -362,7 +427,9 @@ __device__ __forceinline__ void epi_prune8(EpiCtx& e, const TsParams& p, int lan
     const int sorted = p.full_sort ? 0 : __shfl_sync(0xffffffffu, *e.sorted_s, j);
     __syncwarp();
     int keep;
-    const uint64_t kth = warp_prune<E>(e.warp_cand + (size_t)j * kStride, n, p.k, lane, &keep, sorted);
+    uint64_t kth;
+    if (p.full_sort == 2) kth = warp_prune_select<E>(e.warp_cand + (size_t)j * kStride, n, p.k, lane, &keep);
+    else kth = warp_prune<E>(e.warp_cand + (size_t)j * kStride, n, p.k, lane, &keep, sorted);
     if (lane == j) {
       *e.cnt_s = keep;
       *e.sorted_s = keep;
@@ -389,7 +456,7 @@ __device__ __forceinline__ void epi_flush(EpiCtx& e, int64_t qrow0, int split, c
   for (int j = j0; j < 32; j += jstep) {
     const int n = __shfl_sync(0xffffffffu, my_cnt, j);
     uint64_t* base = e.warp_cand + (size_t)j * kStride;
-    uint64_t* out = p.out + ((size_t)(qrow0 + j) * p.n_splits + split) * p.kpad;
+    uint64_t* out = p.out + ((size_t)(qrow0 + j) * p.out_lists + split) * p.kpad;
     const int keep = n < p.k ? n : p.k;
     if constexpr (E == 2) {
       const uint64_t v = warp_top32_of_64(base, n, lane);
@@ -425,7 +492,17 @@ __device__ __forceinline__ void epi_flush(EpiCtx& e, int64_t qrow0, int split, c
 // pair form would run it beside an all-zero query tile, i.e. spend half of every MMA and half of the TMEM reads on
 // nothing.  Such a batch is HBM-bound (128 queries x 2 flop per corpus byte pair), so what matters is corpus bytes in
 // flight per SM — every SM walks its own row split, 32 KB of corpus per stage.  Same epilogue, same keys out.
-template <int E, int kPairStages, bool kQRes = false, bool kEpi8 = false, bool kSolo = false>
+//
+// kPar (k > 32, with kEpi8): the two epilogue warps of a lane quarter split the TILES, not the columns — warp half h
+// drains accumulator h, i.e. every second tile, all 256 columns — and each keeps its OWN candidate buffers (global
+// memory), count and threshold in registers: no shared per-query state, no appends by atomic, no named barriers.
+// Why (cycle counters of the column-split form at 12.5M x 384 bf16 top-100, profiles/r2_pair_wait_stats.txt): an
+// epilogue warp waits for accumulators 58 % of the time on average, yet the MMA warp waits 21 % of its time for an
+// accumulator to be handed back — a 256-key prune takes longer than the one tile of slack the two accumulators give,
+// and the per-tile barriers pass every delay on to the partner warp.  With the tile split a warp has two tile times per
+// accumulator.  The two halves see disjoint tiles, so a query gets two lists per row split (out_lists = 2 * n_splits);
+// they share their running threshold through p.gthr like the row splits do.
+template <int E, int kPairStages, bool kQRes = false, bool kEpi8 = false, bool kSolo = false, bool kPar = false>
 __global__ void __launch_bounds__(kEpi8 ? kPairThreads8 : kGemmThreads, 1)
 gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_x,
                       const TsParams p) {
@@ -433,6 +510,8 @@ gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_co
   // carve: [resident query k-blocks] | stages | candidate buffers | barriers | tmem base   (identical offsets in both CTAs)
   typedef CandCfg<E, kQRes> Cand;
   static_assert(!(kSolo && kQRes), "the solo form streams its query k-blocks");
+  static_assert(!kPar || (kEpi8 && E >= 4), "tile-parity epilogue: 8 epilogue warps, candidate buffers in global memory");
+  constexpr bool kShared = kEpi8 && !kPar;   // the two threads of a query share its buffer (column split)
   constexpr int kStageB = kSolo ? kStageBytes : kQRes ? kStageBytesA : kPairStageBytes;  // bytes per ring stage
   uint8_t* smem = reinterpret_cast<uint8_t*>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   uint8_t* q_base = smem;
@@ -461,7 +540,7 @@ gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_co
 
   if (threadIdx.x == 0) {
     for (int i = 0; i < kPairStages; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
-    for (int i = 0; i < 2; ++i) { mbar_init(&tfull_bar[i], 1); mbar_init(&tempty_bar[i], (kEpi8 ? 16 : 8) / (kSolo ? 2 : 1)); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&tfull_bar[i], 1); mbar_init(&tempty_bar[i], (kShared ? 16 : 8) / (kSolo ? 2 : 1)); }
     mbar_init(q_bar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -584,6 +663,7 @@ gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_co
     const int tid = quarter * 32 + lane;
     const uint32_t lane_base = tmem_base + ((uint32_t)(quarter * 32) << 16);
     EpiCtx e;
+    if constexpr (kPar) cand = p.cand_ws + ((size_t)blockIdx.x * 2 + half) * kGemmM * Cand::stride;
     e.my = cand + (size_t)tid * Cand::stride;
     e.warp_cand = cand + (size_t)(quarter * 32) * Cand::stride;
     e.cnt = 0;
@@ -601,14 +681,14 @@ gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_co
     } else {
       e.cnt_s = qs_cnt + tid; e.sorted_s = qs_sorted + tid; e.thr_s = qs_thr + tid;
     }
-    if constexpr (kEpi8) {
+    if constexpr (kShared) {
       if (half == 0) { *e.cnt_s = 0; *e.sorted_s = 0; *e.thr_s = e.user_fast; }
       named_bar_sync(1 + quarter, 64);
     }
     constexpr int kBlocks = kPairN / 32;                     // tcgen05.ld blocks of 32 columns per tile
-    const int c_lo = kEpi8 ? half * (kBlocks / 2) : 0, c_hi = kEpi8 ? c_lo + kBlocks / 2 : kBlocks;
-    uint32_t acc = 0, aph = 0;
-    for (int64_t t = t0; t < t1; ++t) {
+    const int c_lo = kShared ? half * (kBlocks / 2) : 0, c_hi = kShared ? c_lo + kBlocks / 2 : kBlocks;
+    uint32_t acc = kPar ? (uint32_t)half : 0u, aph = 0;
+    for (int64_t t = t0 + (kPar ? half : 0); t < t1; t += (kPar ? 2 : 1)) {
       const int64_t row0 = p.row_begin + t * kPairN;
       const unsigned gv = e.gthr ? ld_relaxed_u32(e.gthr) : 0u;
       { STAT_T0(); mbar_wait(&tfull_bar[acc], aph); STAT_ADD(5); }
@@ -623,20 +703,20 @@ gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_co
         for (int c = c_lo; c < c_hi; c += 2) {
           tc_wait_ld_dep(ra);
           tc_ld32(taddr + (c + 1) * 32, rb);
-          epi_chunk<false, ChunkCfg<E>::rows, kEpi8>(e, ra, row0 + c * 32, p, lane);
+          epi_chunk<false, ChunkCfg<E>::rows, kShared>(e, ra, row0 + c * 32, p, lane);
           tc_wait_ld_dep(rb);
           if (c + 2 < c_hi) tc_ld32(taddr + (c + 2) * 32, ra);
-          epi_chunk<false, ChunkCfg<E>::rows, kEpi8>(e, rb, row0 + (c + 1) * 32, p, lane);
+          epi_chunk<false, ChunkCfg<E>::rows, kShared>(e, rb, row0 + (c + 1) * 32, p, lane);
         }
       } else {  // valid mask given, or the tile reaches past row_end
 #pragma unroll 1
         for (int c = c_lo; c < c_hi; c += 2) {
           tc_wait_ld_dep(ra);
           tc_ld32(taddr + (c + 1) * 32, rb);
-          epi_chunk<true, ChunkCfg<E>::rows, kEpi8>(e, ra, row0 + c * 32, p, lane);
+          epi_chunk<true, ChunkCfg<E>::rows, kShared>(e, ra, row0 + c * 32, p, lane);
           tc_wait_ld_dep(rb);
           if (c + 2 < c_hi) tc_ld32(taddr + (c + 2) * 32, ra);
-          epi_chunk<true, ChunkCfg<E>::rows, kEpi8>(e, rb, row0 + (c + 1) * 32, p, lane);
+          epi_chunk<true, ChunkCfg<E>::rows, kShared>(e, rb, row0 + (c + 1) * 32, p, lane);
         }
       }
       tc_fence_before();
@@ -645,15 +725,17 @@ gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_co
         if constexpr (kSolo) mbar_arrive(&tempty_bar[acc]);
         else mbar_arrive_cta(&tempty_bar[acc], 0);
       }
-      if ((acc ^= 1) == 0) aph ^= 1;
+      if constexpr (kPar) aph ^= 1;             // this warp half always drains accumulator `half`
+      else if ((acc ^= 1) == 0) aph ^= 1;
       // after the accumulator is handed back: off the MMA's critical path
       { STAT_T0();
-      if constexpr (kEpi8) epi_prune8<E, kQRes>(e, p, lane, quarter, half);
+      if constexpr (kShared) epi_prune8<E, kQRes>(e, p, lane, quarter, half);
       else epi_prune<E, kQRes>(e, p, lane);
       STAT_ADD(6); }
     }
     { STAT_T0();
-    if constexpr (kEpi8) epi_flush<E, kQRes>(e, (int64_t)qt * kGemmM + quarter * 32, split, p, lane, half, 2, true);
+    if constexpr (kShared) epi_flush<E, kQRes>(e, (int64_t)qt * kGemmM + quarter * 32, split, p, lane, half, 2, true);
+    else if constexpr (kPar) epi_flush<E, kQRes>(e, (int64_t)qt * kGemmM + quarter * 32, split * 2 + half, p, lane);
     else epi_flush<E, kQRes>(e, (int64_t)qt * kGemmM + quarter * 32, split, p, lane);
     STAT_ADD(7); }
     STAT_OUT(warp == 2 && lane == 0, 5, 7);

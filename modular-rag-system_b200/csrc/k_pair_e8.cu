@@ -2,7 +2,10 @@
 #include "gemm_pair.cuh"
 #include "kernels.h"
 namespace ragb {
-const void* k_pair_e8(bool qres, bool epi8) {
+const void* k_pair_e8(bool qres, bool epi8, bool par) {
+  if (par)  // tile-parity epilogue (8 warps)
+    return qres ? (const void*)gemm_topk_pair_kernel<8, kPairStagesLargeQ, true, true, false, true>
+                : (const void*)gemm_topk_pair_kernel<8, kPairStagesLarge, false, true, false, true>;
   if (epi8)
     return qres ? (const void*)gemm_topk_pair_kernel<8, kPairStagesLargeQ, true, true> : (const void*)gemm_topk_pair_kernel<8, kPairStagesLarge, false, true>;
   return qres ? (const void*)gemm_topk_pair_kernel<8, kPairStagesLargeQ, true, false> : (const void*)gemm_topk_pair_kernel<8, kPairStagesLarge, false, false>;

@@ -11,10 +11,10 @@ namespace ragb {
 
 // gemm_pair.cuh: gemm_topk_pair_kernel<E, stages, qres, epi8>(CUtensorMap map_q, CUtensorMap map_x, TsParams)
 const void* k_pair_e2(bool qres, bool epi8);
-const void* k_pair_e4(bool qres, bool epi8);
-const void* k_pair_e8(bool qres, bool epi8);
-inline const void* k_pair(int E, bool qres, bool epi8) {
-  return E == 2 ? k_pair_e2(qres, epi8) : E == 4 ? k_pair_e4(qres, epi8) : k_pair_e8(qres, epi8);
+const void* k_pair_e4(bool qres, bool epi8, bool par);   // par: tile-parity epilogue (kPar; implies 8 epilogue warps)
+const void* k_pair_e8(bool qres, bool epi8, bool par);
+inline const void* k_pair(int E, bool qres, bool epi8, bool par) {
+  return E == 2 ? k_pair_e2(qres, epi8) : E == 4 ? k_pair_e4(qres, epi8, par) : k_pair_e8(qres, epi8, par);
 }
 // gemm_pair.cuh, kSolo: gemm_topk_pair_kernel<E, stages, false, true, true> — one CTA, M=128, for a batch of one query tile
 const void* k_solo(int E);

@@ -69,6 +69,7 @@ struct TsParams {
   uint64_t* cand_ws;    // pair kernel, kpad > 32: [grid][128][2*kpad] candidate buffers in global memory
   float sel_slack;      // pair kernel: slack under the user threshold for the 16-bit-query selection pass
   int sync_tiles;       // pair kernel: tiles between two meetings
+  int out_lists;        // pair kernel: lists per query in `out` (n_splits, or 2 * n_splits with the tile-parity epilogue)
   int full_sort;        // pair kernel, k > 32: 1 = every prune sorts the whole buffer (A/B switch RAGB_PAIR_FULLSORT)
   unsigned* gthr;       // pair kernel: [n_qt*128] zeroed per launch, or null — running threshold shared by the row splits
 #ifdef RAGB_PAIR_STATS

@@ -726,7 +726,10 @@ static int gemm_pair_launch(ragb_store* s, SearchCtx* c, const SearchReq& r, cud
   // kpad <= 32: candidate buffers in shared memory, 5-stage ring; kpad 64 / 128: buffers in global memory
   const int E = kpad <= 32 ? 2 : kpad == 64 ? 4 : 8;
   // dim <= 384: the query tile stays in shared memory, the ring carries corpus k-blocks only (gemm_pair.cuh: kQRes)
-  const bool qres = n_kb <= kPairQResMaxKB && env_int("RAGB_PAIR_QRES", 1);
+  // (not for 16 < k <= 32: next to the resident tile a buffer has 48 slots, i.e. k_sel = 32 survivors + the 16 chunks one
+  // tile can add and nothing to spare — every insert forces a prune on the next tile: 1M x 384 B=1024 top-32 1.59 ms
+  // against 0.55 ms for top-10.  With the queries streamed the buffers have 64 slots.)
+  const bool qres = n_kb <= kPairQResMaxKB && (kpad <= 16 || kpad > 32) && env_int("RAGB_PAIR_QRES", 1);
   const int n_stages = qres ? (E == 2 ? kPairStagesSmallQ : kPairStagesLargeQ) : (E == 2 ? kPairStagesSmall : kPairStagesLarge);
   const size_t cand_stride = E == 2 ? (qres ? kPairCapSmallQ : kPairCapSmall) + 1 : 32 * E;
   const size_t smem = 1024 + (qres ? (size_t)n_kb * kStageBytesA + (size_t)n_stages * kStageBytesA : (size_t)n_stages * kPairStageBytes) +
@@ -737,8 +740,18 @@ static int gemm_pair_launch(ragb_store* s, SearchCtx* c, const SearchReq& r, cud
   // bf16 top-100 15.64 -> 15.33 ms per launch; at dim 768, where the tensor pipe was already 97 % busy, 12.32 -> 12.30 ms.
   // RAGB_PAIR_EPI8=0 brings the 4-warp epilogue back for A/B runs.
   const bool epi8 = env_int("RAGB_PAIR_EPI8", 1) != 0;
-  const void* kern = k_pair(E, qres, epi8);
-  const int ei = (E == 2 ? 0 : E == 4 ? 1 : 2) + (qres ? 3 : 0) + (epi8 ? 6 : 0);
+  // k > 32: the two epilogue warps of a lane quarter split the tiles instead of the columns, each with its own candidate
+  // buffers (gemm_pair.cuh: kPar) — two lists per query and row split.  RAGB_PAIR_PAR=0: column split, for A/B runs.
+  // (from two tile pairs up: one pair runs as up to 74 row splits, and 148 lists of 128 keys per query is more than the
+  // finish kernel should have to fold)
+  // Measured (profiles/r2_topk_epilogue_ab.txt): pays on long runs at dim <= 384 (10M x 384 top-64 6.10 -> 5.83 ms,
+  // 12.5M x 384 top-100 14.20 -> 14.06 ms), loses on short ones (each half builds its own top-k: 1M x 384 0.81 -> 0.97 ms)
+  // and at dim 768, where the epilogue has slack anyway.  RAGB_PAIR_PAR=0/1 forces it.
+  const int64_t tiles_per_cta = (r.re - r.rb) / kPairN / std::max(1, (s->n_sm / 2) / std::max(1, n_qt / 2));
+  const int par_env = env_int("RAGB_PAIR_PAR", -1);
+  const bool par = E != 2 && epi8 && n_qt >= 4 && (par_env >= 0 ? par_env != 0 : (qres && tiles_per_cta >= 2000));
+  const void* kern = k_pair(E, qres, epi8, par);
+  const int ei = (E == 2 ? 0 : E == 4 ? 1 : 2) + (qres ? 3 : 0) + (epi8 ? 6 : 0) + (par ? 12 : 0);
   cudaLaunchConfig_t cfg = {};
   cudaLaunchAttribute attr[2];
   cfg.blockDim = dim3(epi8 ? kPairThreads8 : kGemmThreads); cfg.dynamicSmemBytes = smem; cfg.stream = st;
@@ -780,6 +793,7 @@ static int gemm_pair_launch(ragb_store* s, SearchCtx* c, const SearchReq& r, cud
   int splits = std::max(1, clusters / pps);
   if (splits > p.n_tiles) splits = (int)p.n_tiles;
   p.n_splits = splits;
+  p.out_lists = par ? 2 * splits : splits;
   // chunks kept per query: kpad >= k.  With k == kpad there is no spare chunk: a k-th row can lose to a (k+1)-th that
   // scores within the rounding of the 16-bit queries (measured at 1M x 384: 8 / 23 / 49 of 1024 queries for k = 16 /
   // 32 / 128, every swapped row within 3e-5 of the cut — inside the parity band, profiles/r2_parity_ksel_slack_*.json)
@@ -797,14 +811,14 @@ static int gemm_pair_launch(ragb_store* s, SearchCtx* c, const SearchReq& r, cud
     p.sync_ctr = (unsigned*)c->sync_ctr;
     p.sync_tiles = std::max(1, env_int("RAGB_PAIR_SYNC_TILES", kPairSyncTiles));
   }
-  const size_t part_bytes = (size_t)nq_pad * splits * kpad * sizeof(uint64_t);
-  const size_t cand_bytes = E == 2 ? 0 : (size_t)n_qt * splits * kGemmM * (32 * E) * sizeof(uint64_t);
-  const size_t gthr_bytes = (splits > 1 && env_int("RAGB_PAIR_GTHR", 1)) ? (size_t)nq_pad * sizeof(unsigned) : 0;
+  const size_t part_bytes = (size_t)nq_pad * p.out_lists * kpad * sizeof(uint64_t);
+  const size_t cand_bytes = E == 2 ? 0 : (size_t)n_qt * splits * (par ? 2 : 1) * kGemmM * (32 * E) * sizeof(uint64_t);
+  const size_t gthr_bytes = ((splits > 1 || par) && env_int("RAGB_PAIR_GTHR", 1)) ? (size_t)nq_pad * sizeof(unsigned) : 0;
   RB_TRY(grow(&c->ws, &c->ws_bytes, part_bytes + cand_bytes + gthr_bytes, false));
   p.out = (uint64_t*)c->ws;
   p.cand_ws = E == 2 ? nullptr : (uint64_t*)((char*)c->ws + part_bytes);
   p.gthr = nullptr;
-  p.full_sort = env_int("RAGB_PAIR_FULLSORT", 0);
+  p.full_sort = env_int("RAGB_PAIR_FULLSORT", 2);   // 2: prune by selection (gemm_pair.cuh warp_prune_select); 0 / 1: the sorts
   if (gthr_bytes) {  // the row splits of a query share their running threshold (gemm_pair.cuh)
     p.gthr = (unsigned*)((char*)c->ws + part_bytes + cand_bytes);
     CU_TRY(cudaMemsetAsync(p.gthr, 0, gthr_bytes, st));
@@ -861,7 +875,7 @@ static int gemm_pair_launch(ragb_store* s, SearchCtx* c, const SearchReq& r, cud
     }
   }
 #endif
-  return gemm_finish_chunks(s, r, kpad, k_sel, p.out, splits, st);
+  return gemm_finish_chunks(s, r, kpad, k_sel, p.out, p.out_lists, st);
 }
 
 // One query tile (4 <= B <= 128) on every SM by itself (gemm_pair.cuh: kSolo): tcgen05.mma.cta_group::1, M=128 x N=256,
@@ -901,6 +915,7 @@ static int gemm_solo_launch(ragb_store* s, SearchCtx* c, const SearchReq& r, cud
   // a CTA's first tiles run with loose thresholds: give every CTA at least a few tiles before adding CTAs
   int splits = (int)std::min<int64_t>(s->n_sm, std::max<int64_t>(1, p.n_tiles / 4));
   p.n_splits = splits;
+  p.out_lists = splits;
   const int k_sel = kpad;
   p.flags = r.flags; p.threshold = r.threshold; p.k = k_sel; p.kpad = kpad;
   p.sel_slack = s->dtype == RAGB_BF16 ? 8e-3f : 2e-3f;
@@ -914,7 +929,7 @@ static int gemm_solo_launch(ragb_store* s, SearchCtx* c, const SearchReq& r, cud
   p.out = (uint64_t*)c->ws;
   p.cand_ws = E == 2 ? nullptr : (uint64_t*)((char*)c->ws + part_bytes);
   p.gthr = nullptr;
-  p.full_sort = env_int("RAGB_PAIR_FULLSORT", 0);
+  p.full_sort = env_int("RAGB_PAIR_FULLSORT", 2);   // 2: prune by selection (gemm_pair.cuh warp_prune_select); 0 / 1: the sorts
   if (gthr_bytes) {
     p.gthr = (unsigned*)((char*)c->ws + part_bytes + cand_bytes);
     CU_TRY(cudaMemsetAsync(p.gthr, 0, gthr_bytes, st));

@@ -94,8 +94,8 @@ struct GemmShared {
   const void* map_rows = nullptr; int64_t map_capacity = -1;
   const void* ts_rows = nullptr; int64_t ts_capacity = -1; int ts_nt = 0;
   const void* pair_rows = nullptr; int64_t pair_capacity = -1;
-  int pair_clusters[12] = {};
-  bool pair_attr[12] = {};
+  int pair_clusters[24] = {};
+  bool pair_attr[24] = {};
   bool solo_attr[3] = {};
   bool ts_attr[2] = {false, false};
   bool ss_attr = false;

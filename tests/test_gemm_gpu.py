@@ -224,6 +224,37 @@ def test_resident_query_tile_and_shared_threshold_switches(dim, nq, k, monkeypat
     s.close()
 
 
+@pytest.mark.parametrize("dim,nq,k,dtype", [(384, 600, 100, "bf16"), (768, 513, 64, "fp16"), (100, 1100, 128, "fp16")])
+def test_tile_parity_epilogue_equals_column_split(dim, nq, k, dtype, monkeypatch):
+    """k > 32, two tile pairs or more: the two epilogue warps of a lane quarter split the TILES, each with its own
+    candidate buffers and two lists per query and row split (csrc/gemm_pair.cuh kPar; RAGB_PAIR_PAR=0 is the column
+    split).  Both end in the same fp32 re-score of the k_sel best chunks overall: same rows, bit-identical scores —
+    also under a valid mask and a row window that ends inside a tile — and both agree with the oracle."""
+    FORCE_GEMM, _, _ = _flags()
+    rng = np.random.default_rng(dim + nq + k)
+    n = 70_001
+    X = rng.standard_normal((n, dim)).astype(np.float32)
+    X[60_000:60_030] = X[77]                     # ties across tiles of both parities and across row splits
+    Q = rng.standard_normal((nq, dim)).astype(np.float32)
+    Q[0] = X[77] + 0.05 * rng.standard_normal(dim).astype(np.float32)
+    for i in range(3, nq, 13):
+        Q[i] = X[(i * 977) % n] + 0.3 * rng.standard_normal(dim).astype(np.float32)
+    valid = (rng.random(n) > 0.25).astype(np.uint8)
+    s = _store(X, dtype)
+    got = {}
+    for par in ("1", "0"):
+        monkeypatch.setenv("RAGB_PAIR_PAR", par)
+        a = s.search(Q, k, "cosine", flags=FORCE_GEMM)
+        _check(a[0], a[1], X, Q, k, "cosine", -np.inf, False, TOL[dtype])
+        b = s.search(Q, k, "cosine", flags=FORCE_GEMM, valid=valid, row_begin=129, row_end=n - 77, threshold=0.02, clamp01=True)
+        got[par] = [np.array(x) for x in (*a, *b)]
+    for x, y in zip(got["1"], got["0"]):
+        np.testing.assert_array_equal(x, y)
+    top = set(int(x) for x in got["1"][0][0][:31])
+    assert top == ({77} | set(range(60_000, 60_030)))
+    s.close()
+
+
 @pytest.mark.parametrize("k,dtype", [(64, "fp16"), (100, "bf16"), (20, "fp16")])
 def test_masked_epilogue_large_k_vs_oracle(k, dtype):
     """The masked epilogue (valid mask, row window ending inside a tile) of the SM-pair kernel for every candidate-buffer
