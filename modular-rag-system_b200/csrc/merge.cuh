@@ -94,10 +94,9 @@ __global__ void __launch_bounds__(kMergeThreads, RAGB_FINISH_CTAS) finish_chunks
   uint64_t* fin = surv + (size_t)p.kpad * kFinishMaxChunkRows;
   int* misc = reinterpret_cast<int*>(fin + p.kpad);       // [0] survivor count  [1..2] threshold key
 
-  // ---- 1. best k_sel chunks: rank every key by counting (lists are sorted, keys are unique) ----
-  const int n_keys = p.n_lists * p.kpad;
-  const uint64_t* base = p.parts + qi * (int64_t)n_keys;
-  for (int i = threadIdx.x; i < n_keys; i += kMergeThreads) lists[i] = base[i];
+  // ---- 0. what does not depend on the tensor pass: launched with programmatic stream serialization, the CTAs of
+  // this kernel may start while the last CTAs of the kernel that writes p.parts are still draining (csrc/ragb200.cu,
+  // gemm_finish_chunks); griddepcontrol.wait below returns when that kernel has completed and its writes are visible.
   for (int i = threadIdx.x; i < p.kpad; i += kMergeThreads) { chunk[i] = 0; cmax[i] = 0; fin[i] = 0; }
   if (threadIdx.x == 0) { misc[0] = 0; misc[1] = 0; misc[2] = 0; }
   const float* qv = p.q + qi * p.dim;
@@ -108,6 +107,11 @@ __global__ void __launch_bounds__(kMergeThreads, RAGB_FINISH_CTAS) finish_chunks
     qq = warp_sum(qq);
     scale = qq > 0.f ? rsqrtf(qq) : 0.f;  // zero query scores 0.0 everywhere, :214-215
   }
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+  // ---- 1. best k_sel chunks: rank every key by counting (lists are sorted, keys are unique) ----
+  const int n_keys = p.n_lists * p.kpad;
+  const uint64_t* base = p.parts + qi * (int64_t)n_keys;
+  for (int i = threadIdx.x; i < n_keys; i += kMergeThreads) lists[i] = base[i];
   __syncthreads();
   // Bound first: the first m keys of every list (m * n_lists >= k_sel of them) contain at least k_sel keys at or above
   // their k_sel-th largest, L, so the k_sel best keys overall are all >= L and only those need a rank.  With many

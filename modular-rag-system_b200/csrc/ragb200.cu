@@ -708,8 +708,27 @@ static int gemm_finish_chunks(ragb_store* s, const SearchReq& r, int kpad, int k
   const bool small = kpad <= 32 || ChunkCfg<8>::rows == 16;
   const void* kern = k_finish(s->dtype, small ? 16 : 32);
   if (smem > 48 * 1024) CU_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  LAUNCH(kern, dim3((unsigned)r.nq), dim3(kMergeThreads), smem, st, f);
+  // Programmatic dependent launch (RAGB_FINISH_PDL=1): the CTAs may be scheduled while the tensor pass drains
+  // (merge.cuh, step 0).  Measured: no gain (profiles/r2_finish_ab.txt — the persistent tensor-pass CTAs all exit within
+  // microseconds of each other, there is no tail to hide under), and the event behind the tensor pass then also waits
+  // for the early CTAs, which inflates that kernel's bracket.  Off by default.
+  cudaLaunchConfig_t cfg = {};
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.gridDim = dim3((unsigned)r.nq); cfg.blockDim = dim3(kMergeThreads); cfg.dynamicSmemBytes = smem; cfg.stream = st;
+  cfg.attrs = attr; cfg.numAttrs = env_int("RAGB_FINISH_PDL", 0) ? 1 : 0;
+  void* args[] = {(void*)&f};
+  CU_TRY(cudaLaunchKernelExC(&cfg, kern, args));
+  count_launch();
+  CU_TRY(cudaGetLastError());
   return RAGB_OK;
+}
+
+// chunks the tensor pass keeps per query (<= kpad)
+static int ksel_of(int k, int kpad, int E) {
+  static const int spare = env_int("RAGB_KSEL_SPARE", 2);
+  return (E == 2 && spare >= 0) ? std::min(kpad, k + spare) : kpad;
 }
 
 // SM-pair kernel (gemm_pair.cuh): tcgen05.mma.cta_group::2, M=256 (two query tiles) x N=256
@@ -797,7 +816,10 @@ static int gemm_pair_launch(ragb_store* s, SearchCtx* c, const SearchReq& r, cud
   // chunks kept per query: kpad >= k.  With k == kpad there is no spare chunk: a k-th row can lose to a (k+1)-th that
   // scores within the rounding of the 16-bit queries (measured at 1M x 384: 8 / 23 / 49 of 1024 queries for k = 16 /
   // 32 / 128, every swapped row within 3e-5 of the cut — inside the parity band, profiles/r2_parity_ksel_slack_*.json)
-  const int k_sel = kpad;
+  // ... and k + 2 for k <= 32 since r2 (RAGB_KSEL_SPARE, -1 = kpad as before): the finish kernel re-reads 16 rows per
+  // selected chunk, so top-10 with 12 chunks instead of 16 is a quarter fewer bytes there, the running threshold is the
+  // 12th best chunk instead of the 16th, and two spare chunks still cover the 16-bit rounding at the cut
+  const int k_sel = ksel_of(r.k, kpad, E);
   p.flags = r.flags; p.threshold = r.threshold; p.k = k_sel; p.kpad = kpad;
   p.sel_slack = s->dtype == RAGB_BF16 ? 8e-3f : 2e-3f;
   p.id_base = 0;  // chunk keys carry LOCAL start rows; the re-score maps rows to ids
@@ -916,7 +938,7 @@ static int gemm_solo_launch(ragb_store* s, SearchCtx* c, const SearchReq& r, cud
   int splits = (int)std::min<int64_t>(s->n_sm, std::max<int64_t>(1, p.n_tiles / 4));
   p.n_splits = splits;
   p.out_lists = splits;
-  const int k_sel = kpad;
+  const int k_sel = ksel_of(r.k, kpad, E);
   p.flags = r.flags; p.threshold = r.threshold; p.k = k_sel; p.kpad = kpad;
   p.sel_slack = s->dtype == RAGB_BF16 ? 8e-3f : 2e-3f;
   p.id_base = 0;
