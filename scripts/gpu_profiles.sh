@@ -13,12 +13,14 @@ one() { name=$1; regex=$2; skip=$3; shift 3; "$@" > gpurun_out/plain_$name.log 2
 one pair_10Mx768_b1024 gemm_topk_pair 2 python -m scripts.prof_case 10000000 768 1024 4
 one pair_1Mx384_b1024 gemm_topk_pair 2 python -m scripts.prof_case 1000000 384 1024 4
 one pair_12p5Mx384_top100_b4096 gemm_topk_pair 4 python -m scripts.prof_case 12500000 384 4096 4 100 bf16
+one solo_1Mx384_b128 gemm_topk_pair 2 python -m scripts.prof_case 1000000 384 128 4
+one solo_10Mx768_b128 gemm_topk_pair 2 python -m scripts.prof_case 10000000 768 128 4
 one finish_10Mx768_b1024 finish_chunks 2 python -m scripts.prof_case 10000000 768 1024 4
 one finish_1Mx384_b1024 finish_chunks 2 python -m scripts.prof_case 1000000 384 1024 4
 one scan_10Mx768_b1 scan_topk 2 python -m scripts.prof_case 10000000 768 1 4
 one scan_10Mx384_b1 scan_topk 2 python -m scripts.prof_case 10000000 384 1 4
 one scan_1Mx384_b1 scan_topk 2 python -m scripts.prof_case 1000000 384 1 4
-one pool_fp16 pool_norm_pack 4 python scripts/ingest_perf.py
+one pool_fp16 pool_ 4 python scripts/ingest_perf.py
 one norm_pack_f16_f16_384 norm_pack_sub 12 python scripts/norm_pack_perf.py
 rm -f gpurun_out/*.details.csv
 cat gpurun_out/launches_bench_10Mx768_b1024.txt
