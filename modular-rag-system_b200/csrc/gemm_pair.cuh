@@ -26,13 +26,15 @@ namespace ragb {
 // -DRAGB_PAIR_STATS (build variant, scripts/pair_stats.sh): where the warps of a CTA wait, in cycles, per CTA:
 // [0] kernel  [1] producer: empty slot  [2] producer: meeting  [3] MMA: accumulator free  [4] MMA: stage full
 // [5] epilogue warp 2: accumulator full  [6] epilogue warp 2: prune  [7] epilogue warp 2: flush
+// [8] epilogue warp 2: draining a tile  [9..11] inside prune (8 warps): first barrier | prunes | second barrier
+// [12] number of prunes by warp 2  [13] cycles inside the prune function itself
 #ifdef RAGB_PAIR_STATS
 #define STAT_T0() const long long st_t0_ = clock64()
 #define STAT_ADD(i) st_acc_[i] += clock64() - st_t0_
-#define STAT_DECL() long long st_acc_[8] = {0, 0, 0, 0, 0, 0, 0, 0}; const long long st_k0_ = clock64()
+#define STAT_DECL() long long st_acc_[14] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0}; const long long st_k0_ = clock64()
 #define STAT_OUT(cond, lo, hi)                                                                   \
   if ((cond) && p.stats) {                                                                       \
-    for (int i_ = (lo); i_ <= (hi); ++i_) p.stats[(size_t)blockIdx.x * 8 + i_] = st_acc_[i_];   \
+    for (int i_ = (lo); i_ <= (hi); ++i_) p.stats[(size_t)blockIdx.x * 14 + i_] = st_acc_[i_];   \
   }
 #else
 #define STAT_T0()
@@ -308,6 +310,33 @@ __device__ __forceinline__ uint64_t warp_prune_select(uint64_t* base, int n, int
   return m;   // the k-th best key
 }
 
+// Prune of a SHARED-MEMORY buffer (k <= 32, n <= 64 keys) by rank counting: a lane holds up to two keys and counts, for
+// each, the keys of the buffer above it — n broadcast loads, every step independent of the last (the bisection above is
+// a chain of ~15 redux round trips, ~1 400 cycles per prune measured) — and writes the keys of rank < k to slot `rank`:
+// the survivors come out sorted.
+__device__ __forceinline__ uint64_t warp_prune_rank(uint64_t* base, int n, int k, int lane, int* keep_out) {
+  const uint64_t v0 = lane < n ? base[lane] : 0ull, v1 = lane + 32 < n ? base[lane + 32] : 0ull;
+  int r0 = 0, r1 = 0;
+#pragma unroll 4
+  for (int j = 0; j < n; ++j) {
+    const uint64_t kj = base[j];
+    r0 += kj > v0 ? 1 : 0;
+    r1 += kj > v1 ? 1 : 0;
+  }
+  const int keep = n < k ? n : k;
+  *keep_out = keep;
+  __syncwarp();
+  if (lane < n && r0 < keep) base[r0] = v0;
+  if (lane + 32 < n && r1 < keep) base[r1] = v1;
+  // the k-th best key (0 if fewer than k are held)
+  const unsigned b0 = __ballot_sync(0xffffffffu, lane < n && r0 == k - 1);
+  const unsigned b1 = __ballot_sync(0xffffffffu, lane + 32 < n && r1 == k - 1);
+  uint64_t kth = 0ull;
+  if (b0) kth = __shfl_sync(0xffffffffu, v0, __ffs(b0) - 1);
+  else if (b1) kth = __shfl_sync(0xffffffffu, v1, __ffs(b1) - 1);
+  return kth;
+}
+
 // ---- the fused top-k epilogue: CHUNK-granular selection -----------------------------------------
 // Thread == query holds the scores of its query against 32 consecutive rows (two chunks of 16).  The epilogue
 // keeps, per query, the best k_sel CHUNKS (16 consecutive rows) ranked by (chunk maximum, chunk start
@@ -399,7 +428,8 @@ __device__ __forceinline__ void epi_prune(EpiCtx& e, const TsParams& p, int lane
     int keep;
     const int sorted = p.full_sort ? 0 : __shfl_sync(0xffffffffu, e.sorted, j);
     uint64_t kth;
-    if (p.full_sort == 2) kth = warp_prune_select<E>(e.warp_cand + (size_t)j * kStride, n, p.k, lane, &keep);
+    if (E == 2 && p.full_sort == 2) kth = warp_prune_rank(e.warp_cand + (size_t)j * kStride, n, p.k, lane, &keep);
+    else if (p.full_sort == 2) kth = warp_prune_select<E>(e.warp_cand + (size_t)j * kStride, n, p.k, lane, &keep);
     else kth = warp_prune<E>(e.warp_cand + (size_t)j * kStride, n, p.k, lane, &keep, sorted);
     if (lane == j) {
       e.cnt = keep;
@@ -414,22 +444,56 @@ __device__ __forceinline__ void epi_prune(EpiCtx& e, const TsParams& p, int lane
 }
 // kEpi8: the two warps of a lane quarter meet (named barrier: every append of this tile is in the buffers), share the
 // prunes — warp half h takes the queries of its parity — and meet again before the next tile picks up the thresholds
+// non-blocking: has this phase of the barrier completed?
+__device__ __forceinline__ bool mbar_test(uint64_t* bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+  return ok != 0;
+}
+// `next_full` / `next_parity`: the barrier the NEXT accumulator completes.  Besides the prunes that must happen now (a
+// buffer that could overflow during the next tile), a warp prunes buffers that are past half of their spare room for
+// as long as that accumulator has not arrived — the epilogue warps wait for accumulators 40-60 % of the time, while a
+// forced prune in the wrong tile (1 400 cycles and up, against 3 072 tensor cycles per tile at dim 384) is what makes
+// the MMA warp wait for an accumulator (profiles/r2_pair_wait_stats.txt).  RAGB_PAIR_SOFT=0 (p.soft_prune) turns it off.
 template <int E, bool Q>
-__device__ __forceinline__ void epi_prune8(EpiCtx& e, const TsParams& p, int lane, int quarter, int half) {
+__device__ __forceinline__ void epi_prune8(EpiCtx& e, const TsParams& p, int lane, int quarter, int half, uint64_t* next_full,
+                                           uint32_t next_parity, long long* st_acc_ = nullptr) {
   constexpr int kCap = CandCfg<E, Q>::cap, kStride = CandCfg<E, Q>::stride;
+  constexpr int kHard = kCap - kPairN / ChunkCfg<E>::rows;
+#ifdef RAGB_PAIR_STATS
+  long long st_a_ = clock64();
+#endif
   named_bar_sync(1 + quarter, 64);
+#ifdef RAGB_PAIR_STATS
+  { const long long t_ = clock64(); st_acc_[9] += t_ - st_a_; st_a_ = t_; }
+#endif
   const int my_cnt = *e.cnt_s;
-  unsigned need = __ballot_sync(0xffffffffu, my_cnt > kCap - kPairN / ChunkCfg<E>::rows) & (half ? 0xAAAAAAAAu : 0x55555555u);
-  while (need) {
-    const int j = __ffs(need) - 1;
-    need &= need - 1;
+  const unsigned mine = half ? 0xAAAAAAAAu : 0x55555555u;
+  unsigned need = __ballot_sync(0xffffffffu, my_cnt > kHard) & mine;
+  unsigned soft = p.soft_prune ? (__ballot_sync(0xffffffffu, my_cnt > (p.k + kHard) / 2) & mine & ~need) : 0u;
+  for (;;) {
+    int j;
+    if (need) { j = __ffs(need) - 1; need &= need - 1; }
+    else if (soft && !__shfl_sync(0xffffffffu, (int)mbar_test(next_full, next_parity), 0)) { j = __ffs(soft) - 1; soft &= soft - 1; }
+    else break;
     const int n = __shfl_sync(0xffffffffu, my_cnt, j);
     const int sorted = p.full_sort ? 0 : __shfl_sync(0xffffffffu, *e.sorted_s, j);
     __syncwarp();
     int keep;
     uint64_t kth;
-    if (p.full_sort == 2) kth = warp_prune_select<E>(e.warp_cand + (size_t)j * kStride, n, p.k, lane, &keep);
+#ifdef RAGB_PAIR_STATS
+    const long long st_p0_ = clock64();
+#endif
+    if (E == 2 && p.full_sort == 2) kth = warp_prune_rank(e.warp_cand + (size_t)j * kStride, n, p.k, lane, &keep);
+    else if (p.full_sort == 2) kth = warp_prune_select<E>(e.warp_cand + (size_t)j * kStride, n, p.k, lane, &keep);
     else kth = warp_prune<E>(e.warp_cand + (size_t)j * kStride, n, p.k, lane, &keep, sorted);
+#ifdef RAGB_PAIR_STATS
+    st_acc_[12] += 1; st_acc_[13] += clock64() - st_p0_;
+#endif
     if (lane == j) {
       *e.cnt_s = keep;
       *e.sorted_s = keep;
@@ -441,8 +505,14 @@ __device__ __forceinline__ void epi_prune8(EpiCtx& e, const TsParams& p, int lan
     }
     __syncwarp();
   }
+#ifdef RAGB_PAIR_STATS
+  { const long long t_ = clock64(); st_acc_[10] += t_ - st_a_; st_a_ = t_; }
+#endif
   named_bar_sync(1 + quarter, 64);
   e.fthr = fmaxf(e.fthr, *e.thr_s);
+#ifdef RAGB_PAIR_STATS
+  st_acc_[11] += clock64() - st_a_;
+#endif
 }
 
 // sort every query's survivors and write kpad keys
@@ -692,6 +762,9 @@ gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_co
       const int64_t row0 = p.row_begin + t * kPairN;
       const unsigned gv = e.gthr ? ld_relaxed_u32(e.gthr) : 0u;
       { STAT_T0(); mbar_wait(&tfull_bar[acc], aph); STAT_ADD(5); }
+#ifdef RAGB_PAIR_STATS
+      const long long st_d0_ = clock64();
+#endif
       tc_fence_after();
       if (gv) e.fthr = fmaxf(e.fthr, unorder_bits(gv));
       const uint32_t taddr = lane_base + acc * (uint32_t)kPairN;
@@ -721,6 +794,9 @@ gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_co
       }
       tc_fence_before();
       __syncwarp();
+#ifdef RAGB_PAIR_STATS
+      st_acc_[8] += clock64() - st_d0_;
+#endif
       if (lane == 0) {
         if constexpr (kSolo) mbar_arrive(&tempty_bar[acc]);
         else mbar_arrive_cta(&tempty_bar[acc], 0);
@@ -729,7 +805,11 @@ gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_co
       else if ((acc ^= 1) == 0) aph ^= 1;
       // after the accumulator is handed back: off the MMA's critical path
       { STAT_T0();
-      if constexpr (kShared) epi_prune8<E, kQRes>(e, p, lane, quarter, half);
+#ifdef RAGB_PAIR_STATS
+      if constexpr (kShared) epi_prune8<E, kQRes>(e, p, lane, quarter, half, &tfull_bar[acc], aph, st_acc_);
+#else
+      if constexpr (kShared) epi_prune8<E, kQRes>(e, p, lane, quarter, half, &tfull_bar[acc], aph);
+#endif
       else epi_prune<E, kQRes>(e, p, lane);
       STAT_ADD(6); }
     }
@@ -738,11 +818,11 @@ gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_co
     else if constexpr (kPar) epi_flush<E, kQRes>(e, (int64_t)qt * kGemmM + quarter * 32, split * 2 + half, p, lane);
     else epi_flush<E, kQRes>(e, (int64_t)qt * kGemmM + quarter * 32, split, p, lane);
     STAT_ADD(7); }
-    STAT_OUT(warp == 2 && lane == 0, 5, 7);
+    STAT_OUT(warp == 2 && lane == 0, 5, 13);
   }
 
 #ifdef RAGB_PAIR_STATS
-  if (threadIdx.x == 0 && p.stats) p.stats[(size_t)blockIdx.x * 8] = clock64() - st_k0_;
+  if (threadIdx.x == 0 && p.stats) p.stats[(size_t)blockIdx.x * 14] = clock64() - st_k0_;
 #endif
   tc_fence_before();
   __syncthreads();

@@ -70,6 +70,7 @@ struct TsParams {
   float sel_slack;      // pair kernel: slack under the user threshold for the 16-bit-query selection pass
   int sync_tiles;       // pair kernel: tiles between two meetings
   int out_lists;        // pair kernel: lists per query in `out` (n_splits, or 2 * n_splits with the tile-parity epilogue)
+  int soft_prune;       // pair kernel, 8 epilogue warps: prune half-full buffers while the next accumulator is not there yet
   int full_sort;        // pair kernel, k > 32: 1 = every prune sorts the whole buffer (A/B switch RAGB_PAIR_FULLSORT)
   unsigned* gthr;       // pair kernel: [n_qt*128] zeroed per launch, or null — running threshold shared by the row splits
 #ifdef RAGB_PAIR_STATS

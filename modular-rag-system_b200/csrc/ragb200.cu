@@ -841,6 +841,7 @@ static int gemm_pair_launch(ragb_store* s, SearchCtx* c, const SearchReq& r, cud
   p.cand_ws = E == 2 ? nullptr : (uint64_t*)((char*)c->ws + part_bytes);
   p.gthr = nullptr;
   p.full_sort = env_int("RAGB_PAIR_FULLSORT", 2);   // 2: prune by selection (gemm_pair.cuh warp_prune_select); 0 / 1: the sorts
+  p.soft_prune = env_int("RAGB_PAIR_SOFT", 1);
   if (gthr_bytes) {  // the row splits of a query share their running threshold (gemm_pair.cuh)
     p.gthr = (unsigned*)((char*)c->ws + part_bytes + cand_bytes);
     CU_TRY(cudaMemsetAsync(p.gthr, 0, gthr_bytes, st));
@@ -848,8 +849,8 @@ static int gemm_pair_launch(ragb_store* s, SearchCtx* c, const SearchReq& r, cud
   cfg.gridDim = dim3((unsigned)(n_qt * splits));
 #ifdef RAGB_PAIR_STATS
   static long long* stats_dev = nullptr;   // build variant only (scripts/pair_stats.sh): one device, one search at a time
-  if (!stats_dev) CU_TRY(cudaMalloc(&stats_dev, 1024 * 8 * sizeof(long long)));
-  CU_TRY(cudaMemsetAsync(stats_dev, 0, 1024 * 8 * sizeof(long long), st));
+  if (!stats_dev) CU_TRY(cudaMalloc(&stats_dev, 1024 * 14 * sizeof(long long)));
+  CU_TRY(cudaMemsetAsync(stats_dev, 0, 1024 * 14 * sizeof(long long), st));
   p.stats = stats_dev;
 #endif
   void* args[] = {(void*)&map_q, (void*)&map_x, (void*)&p};
@@ -877,20 +878,22 @@ static int gemm_pair_launch(ragb_store* s, SearchCtx* c, const SearchReq& r, cud
   CU_TRY(cudaGetLastError());
 #ifdef RAGB_PAIR_STATS
   if (env_int("RAGB_PAIR_STATS_PRINT", 0)) {
-    static std::vector<long long> h(1024 * 8);
+    static std::vector<long long> h(1024 * 14);
     CU_TRY(cudaStreamSynchronize(st));
     CU_TRY(cudaMemcpy(h.data(), stats_dev, h.size() * sizeof(long long), cudaMemcpyDeviceToHost));
     const int grid = n_qt * splits;
-    double sum[8] = {}, mx[8] = {};
+    double sum[14] = {}, mx[14] = {};
     for (int b = 0; b < grid; ++b)
-      for (int i = 0; i < 8; ++i) {
+      for (int i = 0; i < 14; ++i) {
         if ((i == 3 || i == 4) && (b & 1)) continue;   // the MMA warp works in the leader only
-        sum[i] += (double)h[b * 8 + i]; mx[i] = std::max(mx[i], (double)h[b * 8 + i]);
+        sum[i] += (double)h[b * 14 + i]; mx[i] = std::max(mx[i], (double)h[b * 14 + i]);
       }
-    static const char* names[8] = {"kernel", "producer: empty slot", "producer: meeting", "MMA: accumulator free", "MMA: stage full",
-                                   "epilogue: accumulator full", "epilogue: prune", "epilogue: flush"};
+    static const char* names[14] = {"kernel", "producer: empty slot", "producer: meeting", "MMA: accumulator free", "MMA: stage full",
+                                    "epilogue: accumulator full", "epilogue: prune", "epilogue: flush", "epilogue: draining tiles",
+                                    "  prune: first barrier", "  prune: prunes", "  prune: second barrier", "  prunes (count, warp 2)",
+                                    "  cycles in the prune function"};
     fprintf(stderr, "pair stats: grid %d, E %d, qres %d, tiles per CTA %lld\n", grid, E, (int)qres, (long long)(p.n_tiles / splits));
-    for (int i = 0; i < 8; ++i) {
+    for (int i = 0; i < 14; ++i) {
       const double n = (i == 3 || i == 4) ? grid / 2 : grid;
       fprintf(stderr, "  %-28s mean %12.0f cycles (%5.1f %% of the kernel)  max %12.0f\n", names[i], sum[i] / n,
               100.0 * (sum[i] / n) / (sum[0] / grid), mx[i]);
@@ -952,6 +955,7 @@ static int gemm_solo_launch(ragb_store* s, SearchCtx* c, const SearchReq& r, cud
   p.cand_ws = E == 2 ? nullptr : (uint64_t*)((char*)c->ws + part_bytes);
   p.gthr = nullptr;
   p.full_sort = env_int("RAGB_PAIR_FULLSORT", 2);   // 2: prune by selection (gemm_pair.cuh warp_prune_select); 0 / 1: the sorts
+  p.soft_prune = env_int("RAGB_PAIR_SOFT", 1);
   if (gthr_bytes) {
     p.gthr = (unsigned*)((char*)c->ws + part_bytes + cand_bytes);
     CU_TRY(cudaMemsetAsync(p.gthr, 0, gthr_bytes, st));
