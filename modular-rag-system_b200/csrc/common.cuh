@@ -91,7 +91,11 @@ __device__ __forceinline__ void peer_signal(const PeerOut& po, unsigned n_ctas) 
   // every finishing CTA, which made the peer exchange slower than an NCCL all-gather at 1 024 queries.
   __syncthreads();
   if (threadIdx.x == 0) {
-    __threadfence_system();
+    // signal & 2: the per-CTA fence at GPU scope only.  Causality is transitive across scopes: this CTA's peer stores
+    // are ordered before its ticket at GPU scope, the last CTA observes every ticket and fences at SYSTEM scope before
+    // it publishes the epoch — so a rank that acquires the epoch sees every CTA's keys — and no CTA but the last waits
+    // for its NVLink stores to be acknowledged.
+    if (po.signal & 2) __threadfence(); else __threadfence_system();
     const unsigned t = atomicAdd(po.done, 1u);
     if (t == n_ctas - 1) {
       *po.done = 0;  // everybody else has already arrived: ready for the next launch

@@ -1000,7 +1000,7 @@ static int gemm_pair_search(ragb_store* s, SearchCtx* c, const SearchReq& r, cud
     if (r.out_ids) g.out_ids = r.out_ids + (size_t)q0 * r.k;
     if (r.peer.n) {  // this group's slot inside every rank's gather buffer; only the last group publishes the epoch
       for (int p = 0; p < g.peer.n; ++p) g.peer.keys[p] += (size_t)q0 * kpad;
-      g.peer.signal = (q0 + step >= r.nq) ? 1 : 0;
+      g.peer.signal = (q0 + step >= r.nq) ? r.peer.signal : 0;
     }
     rc = gemm_pair_launch(s, c, g, st);
   }
@@ -1498,7 +1498,7 @@ extern "C" int ragb_search_scatter_dev(ragb_store* s, const float* q, int64_t nq
   SearchReq r;
   r.q = q; r.nq = nq; r.k = k; r.metric = metric; r.threshold = threshold; r.flags = flags; r.valid = valid;
   r.id_base = id_base;
-  r.peer.n = x->world; r.peer.epoch = x->epoch; r.peer.signal = 1;
+  r.peer.n = x->world; r.peer.epoch = x->epoch; r.peer.signal = 1 | (env_int("RAGB_PEER_GPUFENCE", 1) ? 2 : 0);
   for (int p = 0; p < x->world; ++p) {
     r.peer.keys[p] = x->keys[p] + (size_t)x->rank * nq * kpad;  // this rank's [nq][kpad] slot in rank p's buffer
     r.peer.flag[p] = x->flags[p] + x->rank;
@@ -1546,7 +1546,7 @@ extern "C" int ragb_search_exchange(ragb_store* s, const float* q, int64_t nq, i
   SearchReq r;
   r.q = (const float*)d; r.nq = nq; r.k = k; r.metric = metric; r.threshold = threshold; r.flags = flags;
   r.rb = rb; r.re = re; r.id_base = id_base;
-  r.peer.n = x->world; r.peer.epoch = x->epoch; r.peer.signal = 1; r.peer.done = c->tickets + kScanMaxQ;
+  r.peer.n = x->world; r.peer.epoch = x->epoch; r.peer.signal = 1 | (env_int("RAGB_PEER_GPUFENCE", 1) ? 2 : 0); r.peer.done = c->tickets + kScanMaxQ;
   for (int p = 0; p < x->world; ++p) {
     r.peer.keys[p] = x->keys[p] + (size_t)x->rank * nq * kpad;
     r.peer.flag[p] = x->flags[p] + x->rank;
