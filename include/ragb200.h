@@ -9,7 +9,9 @@
  * Conventions
  *   - every function returns 0 on success, a negative RAGB_E* code on failure;
  *     ragb_last_error() gives a thread-local message.  Nothing throws.
- *   - "host" entry points take plain host pointers and copy; "_dev" entry
+ *   - "host" entry points take plain host pointers and copy (query buffers that are page-locked — cudaHostAlloc /
+ *     cudaHostRegister, e.g. a torch pinned tensor — are read by the copy engine in place, pageable ones are staged
+ *     through pinned memory in pieces; either way the call returns only when the buffers may be reused); "_dev" entry
  *     points take device pointers on the store's GPU plus a cudaStream_t passed
  *     as void* (NULL = the store's own stream, synchronised before return; to run on the legacy default stream
  *     asynchronously pass cudaStreamLegacy, i.e. (void*)1).

@@ -368,6 +368,7 @@ static int msearch(ragb_mstore* m, const float* q_host, const float* q_dev, int6
   for (int d = 0; d < G; ++d) { leases.emplace_back(new CtxLease(m->st[d])); RB_TRY(leases[d]->acquire()); }
   const bool caller = stream != nullptr;
   cudaStream_t st0 = caller ? (cudaStream_t)stream : leases[0]->c->stream;
+  const void* q_src = nullptr;
   {
     ON_DEVICE(m->dev[0]);
     RB_TRY(grow(&mc->gather, &mc->gather_bytes, (size_t)G * nq * kpad * 8, false));
@@ -375,7 +376,10 @@ static int msearch(ragb_mstore* m, const float* q_host, const float* q_dev, int6
     if (q_host) {
       RB_TRY(grow(&mc->io, &mc->io_bytes, al(sb) + al(ib), false));
       RB_TRY(grow(&mc->pin, &mc->pin_bytes, al(qb) + al(sb) + al(ib), true));
-      memcpy(mc->pin, q_host, qb);
+      // a page-locked source is uploaded to every shard in place; a pageable one once through the pinned buffer
+      cudaPointerAttributes pa;
+      if (cudaPointerGetAttributes(&pa, q_host) == cudaSuccess && pa.type == cudaMemoryTypeHost) q_src = q_host;
+      else { (void)cudaGetLastError(); memcpy(mc->pin, q_host, qb); q_src = mc->pin; }
     } else {
       CU_TRY(cudaEventRecord(mc->start, st0));  // the queries are ready on the first device from here on
     }
@@ -394,7 +398,7 @@ static int msearch(ragb_mstore* m, const float* q_host, const float* q_dev, int6
     if (q_host) {
       const size_t vb = (valid && !use_filter) ? (size_t)re : 0;
       RB_TRY(grow(&c->io, &c->io_bytes, al(qb) + al(vb), false));
-      CU_TRY(cudaMemcpyAsync(c->io, mc->pin, qb, cudaMemcpyHostToDevice, st));
+      CU_TRY(cudaMemcpyAsync(c->io, q_src, qb, cudaMemcpyHostToDevice, st));
       r.q = (const float*)c->io;
       if (vb) {  // de-interleave the global mask into this shard's local rows (block pieces)
         RB_TRY(grow(&c->pin, &c->pin_bytes, vb, true));

@@ -41,6 +41,25 @@ int grow(void** p, size_t* have, size_t need, bool pinned) {
   *have = want;
   return RAGB_OK;
 }
+int upload_host(void* dev, void* pin, const void* src, size_t bytes, cudaStream_t st) {
+  if (bytes == 0) return RAGB_OK;
+  cudaPointerAttributes a;
+  if (cudaPointerGetAttributes(&a, src) == cudaSuccess) {
+    if (a.type == cudaMemoryTypeHost) {   // page-locked already: no staging copy
+      CU_TRY(cudaMemcpyAsync(dev, src, bytes, cudaMemcpyHostToDevice, st));
+      return RAGB_OK;
+    }
+  } else {
+    (void)cudaGetLastError();
+  }
+  const size_t piece = bytes <= ((size_t)256 << 10) ? bytes : (size_t)512 << 10;
+  for (size_t o = 0; o < bytes; o += piece) {
+    const size_t m = std::min(piece, bytes - o);
+    memcpy((char*)pin + o, (const char*)src + o, m);
+    CU_TRY(cudaMemcpyAsync((char*)dev + o, (char*)pin + o, m, cudaMemcpyHostToDevice, st));
+  }
+  return RAGB_OK;
+}
 }  // namespace ragb
 #define LAUNCH(...)                                                                                          \
   do {                                                                                                       \
@@ -1540,9 +1559,8 @@ extern "C" int ragb_search_exchange(ragb_store* s, const float* q, int64_t nq, i
   char* d = (char*)c->io;
   char* h = (char*)c->pin;
   RB_TRY(store_prepare_stream(s, c, c->stream, false));
-  memcpy(h, q, qb);
   *(int*)(h + o_st) = 0;
-  CU_TRY(cudaMemcpyAsync(d, h, qb, cudaMemcpyHostToDevice, c->stream));
+  RB_TRY(upload_host(d, h, q, qb, c->stream));
   SearchReq r;
   r.q = (const float*)d; r.nq = nq; r.k = k; r.metric = metric; r.threshold = threshold; r.flags = flags;
   r.rb = rb; r.re = re; r.id_base = id_base;
@@ -1599,14 +1617,14 @@ extern "C" int ragb_search(ragb_store* s, const float* q, int64_t nq, int k, int
   char* d = (char*)c->io;
   char* h = (char*)c->pin;
   RB_TRY(store_prepare_stream(s, c, c->stream, false));
-  memcpy(h, q, qb);
   // Small calls are all latency (BASELINE configs[0]: one query against 10k rows): pinned host memory is mapped into the
   // device's address space, so the kernels can read the queries from it and write the k winners straight into it —
   // no copy engine round trips on either side of the launch.  RAGB_ZERO_COPY: bit 0 = results, bit 1 = queries.
   static const int zc = env_int("RAGB_ZERO_COPY", 1);
   const bool zc_out = (zc & 1) && sb + ib <= 65536;
   const bool zc_in = (zc & 2) && qb <= 16384;
-  if (!zc_in) CU_TRY(cudaMemcpyAsync(d, h, qb, cudaMemcpyHostToDevice, c->stream));
+  if (zc_in) memcpy(h, q, qb);
+  else RB_TRY(upload_host(d, h, q, qb, c->stream));
   if (valid) CU_TRY(cudaMemcpyAsync(d + o_v, valid, vb, cudaMemcpyHostToDevice, c->stream));
   SearchReq r;
   r.q = (const float*)(zc_in ? h : d); r.nq = nq; r.k = k; r.metric = metric; r.threshold = threshold; r.flags = flags;

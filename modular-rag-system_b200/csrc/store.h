@@ -50,6 +50,11 @@ struct DeviceGuard {
                                       cudaGetErrorString(cudaGetLastError()))
 
 int grow(void** p, size_t* have, size_t need, bool pinned);
+// Host buffer -> device on `st`.  A page-locked source (cudaHostAlloc / cudaHostRegister, e.g. a torch pinned tensor) is
+// read by the copy engine in place; a pageable one is staged through `pin` (page-locked, >= bytes) in pieces, so that
+// the copy engine moves piece i while the host copies piece i + 1 (3 MB of queries: the two no longer add up).
+// The call returns with copies queued; the caller synchronises the stream before the source may change.
+int upload_host(void* dev, void* pin, const void* src, size_t bytes, cudaStream_t st);
 inline size_t elem_size(int dtype) { return dtype == RAGB_F32 ? 4 : 2; }
 
 // launch through a `const void*` entry point (kernels.h); argument types must be the kernel's own

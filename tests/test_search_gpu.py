@@ -238,3 +238,27 @@ def test_concurrent_readers_overlap():
     print(f"queries/s: 1 thread {one:.0f}, 8 threads {eight:.0f} ({eight / one:.2f}x)")
     assert eight > 1.5 * one, (one, eight)
     s.close()
+
+
+def test_page_locked_and_pageable_host_queries_agree():
+    """ragb_search / ragb_mstore_search hand a page-locked query buffer (cudaHostAlloc, e.g. a torch pinned tensor) to the
+    copy engine in place and stage a pageable one through pinned memory in pieces (csrc/ragb200.cu upload_host): same
+    results either way, for a batch larger than one piece and for a single query."""
+    import torch
+    from modular_rag_system_b200 import DeviceStore, ShardedDeviceStore
+    rng = np.random.default_rng(5)
+    n, d = 30_000, 384
+    X = rng.standard_normal((n, d)).astype(np.float32)
+    s = DeviceStore(d, "fp16", n)
+    s.add(X)
+    ms = ShardedDeviceStore(d, "fp16", n, [0, 0], block_rows=4096)
+    ms.add(X)
+    for nq in (1, 700):                                  # 700 x 384 x 4 B = 1.07 MB: three pieces
+        Q = rng.standard_normal((nq, d)).astype(np.float32)
+        Qp = torch.from_numpy(Q).pin_memory().numpy()
+        a, b = s.search(Q, 10, "cosine"), s.search(Qp, 10, "cosine")
+        assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1])
+        c, e = ms.search(Q, 10, "cosine"), ms.search(Qp, 10, "cosine")
+        assert np.array_equal(c[0], e[0]) and np.array_equal(c[1], e[1]) and np.array_equal(a[0], c[0])
+    ms.close()
+    s.close()
