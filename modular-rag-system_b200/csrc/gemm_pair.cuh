@@ -529,7 +529,14 @@ __device__ __forceinline__ void epi_flush(EpiCtx& e, int64_t qrow0, int split, c
     uint64_t* out = p.out + ((size_t)(qrow0 + j) * p.out_lists + split) * p.kpad;
     const int keep = n < p.k ? n : p.k;
     if constexpr (E == 2) {
-      const uint64_t v = warp_top32_of_64(base, n, lane);
+      uint64_t v;
+      if (n <= 32) {   // the usual case after the last tile's prune: one key per lane, sorted in registers
+        uint64_t v1[1] = {lane < n ? base[lane] : 0ull};
+        warp_sort_desc<1>(v1, lane);
+        v = v1[0];
+      } else {
+        v = warp_top32_of_64(base, n, lane);
+      }
       if (lane < p.kpad) out[lane] = lane < keep ? v : 0ull;
     } else {
       const int sorted = p.full_sort ? 0 : __shfl_sync(0xffffffffu, my_sorted, j);
