@@ -8,13 +8,19 @@
 // the ring holds 5 stages instead of 3 next to the candidate buffers, and it keeps the pair in lock
 // step by construction (the leader's commit releases the stage in both CTAs).
 //
-// Roles per CTA (192 threads, 1 CTA/SM):
-//   warp 0    producer : TMA (cp.async.bulk.tensor ... cta_group::2) of the own query k-block and the
-//                        own half of the corpus k-block; bytes are accounted on the LEADER's barrier
+// Roles per CTA (320 threads by default — kEpi8 — or 192; 1 CTA/SM):
+//   warp 0    producer : TMA (cp.async.bulk.tensor ... cta_group::2) of the own query k-block (or, kQRes, the whole
+//                        query tile once) and the own half of the corpus k-block; bytes are accounted on the LEADER's
+//                        barrier
 //   warp 1    MMA      : leader CTA only; one elected lane issues tcgen05.mma.cta_group::2 and
 //                        multicasts tcgen05.commit to both CTAs' barriers
-//   warps 2-5 epilogue : as in gemm_ts.cuh (thread == query == TMEM lane); "accumulator drained"
-//                        arrives on the leader's barrier from both CTAs (mapa + mbarrier.arrive)
+//   warps 2-9 epilogue : thread == query == TMEM lane; two warps per lane quarter, splitting the accumulator's columns
+//                        (shared per-query state, named barriers) or — kPar — the tiles (private state);
+//                        "accumulator drained" arrives on the leader's barrier from both CTAs (mapa + mbarrier.arrive).
+//                        Chunk-granular selection, prune by rank counting / bisection, flush at the end (below).
+// Forms of the one template: pair (this header's title), kSolo (one CTA, cta_group::1, a batch of one query tile),
+// kQRes (resident query tile, dim <= 384), kEpi8 / kPar (epilogue organisation), E (candidate buffers: shared memory for
+// k <= 32, global memory for k <= 64 / 128).  -DRAGB_PAIR_STATS adds cycle counters around every wait.
 //
 // The reference has no batched path (callers loop RAGVectorStore.search,
 // ollama_rag_system.py:388-403 / :480-515); per query the result is the same scan.
