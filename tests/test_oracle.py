@@ -129,3 +129,76 @@ def test_full_size_parity_helper_equals_plain_oracle(dtype):
     s1[13, 6] = s1[13, 7]                              # smallest k / k+1 gap
     pick = parity.sample_queries(s1, 7, 10, always=[39])
     assert 39 in pick and 13 in pick and len(pick) == 10
+
+
+def _live_reference():
+    """The UNMODIFIED reference module from oracle/_ref (SHA-256 checked copy, oracle/fetch_ref.py), or None."""
+    import contextlib
+    import importlib.util
+    import io
+    from pathlib import Path
+    import oracle
+    d = oracle.ref_path()            # None unless the copy is bit-identical to the surveyed reference
+    if d is None:
+        return None
+    p = Path(d) / "ollama_rag_system.py"
+    spec = importlib.util.spec_from_file_location("_ref_ollama_rag_system_live", p)
+    mod = importlib.util.module_from_spec(spec)
+    with contextlib.redirect_stdout(io.StringIO()):
+        spec.loader.exec_module(mod)
+    return mod
+
+
+@pytest.mark.parametrize("seed", range(12))
+def test_oracle_equals_unmodified_reference_on_random_stores(seed, tmp_path):
+    """Beyond the committed fixtures: random small stores — duplicate rows (exact ties), zero rows, negative cosines,
+    replaced ids, NULL embeddings, source filters, out-of-order timestamps, random k and threshold — through the
+    unmodified RAGVectorStore.search (:388-525) and through the oracle under the same policy: same rows in the same
+    order, similarities equal to 1e-12.  Runs wherever oracle/_ref exists (this container, the GPU box)."""
+    import contextlib
+    import io
+    from pathlib import Path
+    R = _live_reference()
+    if R is None:
+        pytest.skip("oracle/_ref not present (python oracle/fetch_ref.py)")
+    rng = np.random.default_rng(1000 + seed)
+    n = int(rng.integers(0, 90))
+    d = int(rng.choice([16, 128]))
+    k = int(rng.integers(1, 13))
+    thr = float(rng.choice([0.0, 0.05, 0.2, 0.7]))
+    X = rng.standard_normal((n, d)).astype(np.float32)
+    if n > 8:
+        X[5] = X[2]; X[n - 1] = X[2]          # exact ties
+        X[3] = 0.0                             # zero norm: scores 0.0 (:214-215)
+        X[6] = -X[2]                           # negative cosine, clamped to 0 (:218)
+    q = (X[2] + 0.2 * rng.standard_normal(d)).astype(np.float32) if n > 8 else rng.standard_normal(d).astype(np.float32)
+    if seed % 5 == 4:
+        q[:] = 0.0                             # zero query
+    ts = 1000.0 + np.arange(n, dtype=np.float64)
+    if seed % 3 == 1 and n > 4:
+        ts = rng.permutation(ts)               # out-of-order timestamps
+    doc_ids = np.array([f"d{i}" for i in range(n)])
+    if n > 12:
+        doc_ids[10] = "d4"                     # replaces row 4 (INSERT OR REPLACE, :351)
+    sources = np.array([("a", "b", "c")[i % 3] for i in range(n)])
+    sf = ["a", "c"] if seed % 4 == 2 else []
+    null_rows = np.array([7], dtype=np.int64) if n > 9 and seed % 2 == 0 else np.zeros(0, np.int64)
+    with contextlib.redirect_stdout(io.StringIO()):
+        vs = R.RAGVectorStore(Path(tmp_path))
+        for i in range(n):
+            emb = None if i in null_rows else X[i].astype(np.float64).tolist()
+            doc = R.RAGDocument(id=str(doc_ids[i]), content=f"chunk {i}", metadata={"i": i}, embedding=emb,
+                                timestamp=float(ts[i]), source=str(sources[i]))
+            assert (vs._add_document_sqlite(doc) if emb is None else vs.add_document(doc))
+        vs.embedding_generator.embedding_cache["Q"] = q.astype(np.float64).tolist()
+        res = vs.search(R.RAGQuery(query_text="Q", context={}, max_results=k, similarity_threshold=thr,
+                                   source_filters=sf or None))
+    last = {str(did): i for i, did in enumerate(doc_ids)}
+    ref_rows = [last[doc.id] for doc in res.documents]
+    ref_sims = [float(s) for s in res.similarities]
+    fx = {"X": X, "q": q, "ts": ts, "doc_ids": doc_ids, "sources": sources, "source_filters": np.array(sf),
+          "null_rows": null_rows, "k": k, "thr": thr}
+    rows, sims, total = oracle_policy_search(fx)
+    assert total == res.total_documents_searched
+    assert rows.tolist() == ref_rows
+    np.testing.assert_allclose(sims, ref_sims, rtol=0, atol=1e-12)
